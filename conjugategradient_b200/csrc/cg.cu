@@ -1,0 +1,266 @@
+// cg.cu — the CG solve: host orchestration of the gated iteration kernels.
+// Interface replaced: CGSolver::CG::solve (reference src/CG.hpp:255-454).  The reference submits
+// 12 device operations and one wait_and_throw per iteration; here a batch of iterations is one
+// CUDA-graph launch and the stop flag lives on the device, polled once per batch.
+#include "launch.cuh"
+
+#include <algorithm>
+#include <vector>
+
+using namespace cgb;
+
+namespace cgb {
+
+struct LoopCfg {
+  bool fused;
+  bool time_kernels;
+  int lanes;
+  int grid_spmv;
+  int grid_vec;
+};
+
+// Enqueue one CG iteration on `s`.  When `timed`, bracket the kernels with external event records
+// (legal inside stream capture; they become event-record nodes of the graph).
+static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream_t s, bool timed) {
+  Workspace &w = A->ws;
+  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  auto mark = [&](int i) -> cudaError_t {
+    return timed ? cudaEventRecordWithFlags(w.ev[i], s, cudaEventRecordExternal) : cudaSuccess;
+  };
+  CGB_CUDA(mark(0));
+  if (!c.fused) cg_pupdate_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
+  CGB_CUDA(mark(1));
+  CGB_LAUNCH_LB(c.lanes, c.fused, cg_spmv_kernel, c.grid_spmv, s, V, w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
+                (double *)nullptr);
+  CGB_CUDA(mark(2));
+  if (c.fused)
+    cg_update_kernel<true><<<c.grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
+                                                          (const double *)nullptr, (double *)nullptr);
+  else
+    cg_update_kernel<false><<<c.grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
+                                                           (const double *)nullptr, (double *)nullptr);
+  CGB_CUDA(mark(3));
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
+static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint64_t key) {
+  Workspace &w = A->ws;
+  cudaStream_t s = A->ctx->stream;
+  if (w.graph && w.graph_key == key && w.graph_x == x) return CGB_OK;
+  if (w.graph) {
+    cudaGraphExecDestroy(w.graph);
+    w.graph = nullptr;
+  }
+  cudaGraph_t g = nullptr;
+  CGB_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  int rc = CGB_OK;
+  for (int i = 0; i < batch && rc == CGB_OK; i++) rc = enqueue_iteration(A, x, c, s, c.time_kernels && i == 0);
+  cudaError_t e = cudaStreamEndCapture(s, &g);
+  if (rc != CGB_OK) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+  e = cudaGraphInstantiate(&w.graph, g, 0);
+  cudaGraphDestroy(g);
+  if (e != cudaSuccess) {
+    w.graph = nullptr;
+    return fail(CGB_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+  }
+  w.graph_key = key;
+  w.graph_x = x;
+  return CGB_OK;
+}
+
+} // namespace cgb
+
+extern "C" {
+
+void cgb_cg_default_opts(cgb_cg_opts *o) {
+  if (!o) return;
+  memset(o, 0, sizeof(*o));
+  o->loop_mode = CGB_LOOP_AUTO;
+  o->check_every = 0;
+  o->fuse_p_update = 0;
+}
+
+int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,
+                 const cgb_cg_opts *opts_in, cgb_cg_stats *stats) {
+  CGB_REQUIRE(ctx, "cgb_cg_solve: ctx is NULL");
+  if (!A) return fail(CGB_ERR_STATE, "No Matrix given");                    // src/CG.hpp:270-272
+  if (!d_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");  // src/CG.hpp:266-268
+  CGB_REQUIRE(d_x, "cgb_cg_solve: x is NULL");
+  CGB_REQUIRE(A->ctx == ctx, "cgb_cg_solve: matrix belongs to another context");
+  cgb_cg_opts o;
+  if (opts_in) o = *opts_in; else cgb_cg_default_opts(&o);
+  if (stats) memset(stats, 0, sizeof(*stats));
+  const int64_t n = A->n;
+  if (max_iter < 0) max_iter = n + 1; // reference cap (src/CG.hpp:436)
+  if (n == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  cudaStream_t s = ctx->stream;
+
+  int mode = o.loop_mode;
+  if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = CGB_LOOP_GRAPH;
+  int batch = o.check_every > 0 ? o.check_every : 32;
+  if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
+  const bool fused = o.fuse_p_update != 0;
+  const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
+  CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
+  Workspace &w = A->ws;
+  LoopCfg cfg{fused, o.time_kernels != 0, A->lanes, A->grid_spmv, A->grid_vec};
+  if (cfg.time_kernels)
+    for (auto &e : w.ev)
+      if (!e) CGB_CUDA(cudaEventCreate(&e));
+
+  cudaEvent_t t0, t1;
+  CGB_CUDA(cudaEventCreate(&t0));
+  CGB_CUDA(cudaEventCreate(&t1));
+  struct EvGuard {
+    cudaEvent_t a, b;
+    ~EvGuard() {
+      cudaEventDestroy(a);
+      cudaEventDestroy(b);
+    }
+  } guard{t0, t1};
+
+  CGB_CUDA(cudaEventRecord(t0, s));
+  // state + work vectors (reference: src/CG.hpp:276-301)
+  CgState init;
+  memset(&init, 0, sizeof(init));
+  init.tol = abs_tol;
+  init.max_iter = max_iter;
+  init.record_history = o.record_history ? 1 : 0;
+  init.hist_cap = w.hist_cap;
+  init.done = 1; // K0 arms the loop; until then nothing may run
+  w.h_st[0] = init;
+  CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
+  CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)n, s));
+  if (fused) CGB_CUDA(cudaMemsetAsync(w.p1, 0, sizeof(double) * (size_t)n, s));
+  CsrView V{n, A->rowptr, A->cols, A->vals};
+  CGB_LAUNCH_L(A->lanes, cg_init_kernel, A->grid_spmv, s, V, (const double *)d_x, d_b, w.r, w.st, w.partials, w.hist);
+  CGB_CUDA(cudaGetLastError());
+  int64_t launches = 1;
+
+  const int per_iter = fused ? 2 : 3;
+  double t_p = 0, t_s = 0, t_u = 0;
+  int64_t samples = 0;
+  if (mode == CGB_LOOP_GRAPH) {
+    const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.lanes << 8) ^ ((uint64_t)fused << 1) ^
+                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.grid_spmv << 16);
+    CGB_TRY(build_graph(A, d_x, cfg, batch, key));
+  }
+  // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an
+  // overshooting batch return at once because the state says done.
+  cudaEvent_t polled[2];
+  CGB_CUDA(cudaEventCreateWithFlags(&polled[0], cudaEventDisableTiming));
+  CGB_CUDA(cudaEventCreateWithFlags(&polled[1], cudaEventDisableTiming));
+  EvGuard guard2{polled[0], polled[1]};
+  const bool pipelined = !cfg.time_kernels;
+  int64_t issued = 0; // iterations issued so far
+  int slot = 0;
+  bool finished = false;
+  bool have_prev = false;
+  bool prev_active_at_start = true;
+  while (!finished) {
+    // issue one batch
+    if (mode == CGB_LOOP_GRAPH) {
+      CGB_CUDA(cudaGraphLaunch(w.graph, s));
+    } else {
+      for (int i = 0; i < batch; i++) CGB_TRY(enqueue_iteration(A, d_x, cfg, s, cfg.time_kernels && i == 0));
+    }
+    launches += (int64_t)batch * per_iter;
+    issued += batch;
+    CGB_CUDA(cudaMemcpyAsync(&w.h_st[slot], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+    CGB_CUDA(cudaEventRecord(polled[slot], s));
+    int check = slot;
+    if (pipelined) {
+      if (!have_prev) { // nothing to look at yet: go issue the second batch
+        have_prev = true;
+        slot ^= 1;
+        if (issued < max_iter) continue;
+      } else {
+        check = slot ^ 1;
+      }
+    }
+    CGB_CUDA(cudaEventSynchronize(polled[check]));
+    const CgState &h = w.h_st[check];
+    if (cfg.time_kernels) {
+      if (prev_active_at_start) {
+        float a = 0, b = 0, c = 0;
+        CGB_CUDA(cudaEventElapsedTime(&a, w.ev[0], w.ev[1]));
+        CGB_CUDA(cudaEventElapsedTime(&b, w.ev[1], w.ev[2]));
+        CGB_CUDA(cudaEventElapsedTime(&c, w.ev[2], w.ev[3]));
+        t_p += a; t_s += b; t_u += c;
+        samples++;
+      }
+      prev_active_at_start = !(h.done || h.iter >= h.max_iter);
+    }
+    if (h.done || h.iter >= h.max_iter) finished = true;
+    slot ^= 1;
+  }
+  // drain whatever was issued ahead and take the final state
+  CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+  CGB_CUDA(cudaEventRecord(t1, s));
+  CGB_CUDA(cudaEventSynchronize(t1));
+  const CgState &f = w.h_st[0];
+  w.hist_count = o.record_history ? std::min<int64_t>(f.iter + 1, w.hist_cap) : 0;
+  if (stats) {
+    float ms = 0.f;
+    CGB_CUDA(cudaEventElapsedTime(&ms, t0, t1));
+    stats->iterations = f.iter;
+    stats->rr = f.rr;
+    stats->rr0 = f.rr0;
+    stats->converged = f.done;
+    stats->nan_stop = f.nan_stop;
+    stats->solve_ms = ms;
+    stats->timed_samples = samples;
+    if (samples > 0) {
+      stats->pupdate_ms = t_p / samples;
+      stats->spmv_ms = t_s / samples;
+      stats->update_ms = t_u / samples;
+    }
+    stats->kernel_launches = launches;
+    stats->loop_mode = mode;
+    stats->format = CGB_FMT_CSR;
+  }
+  return CGB_OK;
+}
+
+int cgb_cg_solve_host(cgb_ctx *ctx, int64_t n, int64_t nnz, const double *h_vals, const int32_t *h_cols,
+                      const int32_t *h_rowptr, const double *h_b, const double *h_x0, double *h_x, double abs_tol,
+                      int64_t max_iter, const cgb_cg_opts *opts, cgb_cg_stats *stats) {
+  CGB_REQUIRE(ctx && h_x, "cgb_cg_solve_host: NULL argument");
+  if (!h_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");
+  if (!h_rowptr) return fail(CGB_ERR_STATE, "No Matrix given");
+  ScopedDevice sd(ctx->device);
+  cgb_csr *A = nullptr;
+  CGB_TRY(cgb_csr_create(ctx, n, nnz, h_vals, h_cols, h_rowptr, &A));
+  double *d_b = nullptr, *d_x = nullptr;
+  int rc = cgb_malloc(ctx, sizeof(double) * (size_t)n, (void **)&d_b);
+  if (rc == CGB_OK) rc = cgb_malloc(ctx, sizeof(double) * (size_t)n, (void **)&d_x);
+  if (rc == CGB_OK) rc = cgb_memcpy_h2d(ctx, d_b, h_b, sizeof(double) * (size_t)n, 0);
+  if (rc == CGB_OK)
+    rc = h_x0 ? cgb_memcpy_h2d(ctx, d_x, h_x0, sizeof(double) * (size_t)n, 0)
+              : cgb_memset(ctx, d_x, 0, sizeof(double) * (size_t)n); // x defaults to zeros (src/CG.hpp:291-297)
+  if (rc == CGB_OK) rc = cgb_cg_solve(ctx, A, d_b, d_x, abs_tol, max_iter, opts, stats);
+  if (rc == CGB_OK) rc = cgb_memcpy_d2h(ctx, h_x, d_x, sizeof(double) * (size_t)n, 1);
+  cgb_free(ctx, d_b);
+  cgb_free(ctx, d_x);
+  cgb_csr_destroy(A);
+  return rc;
+}
+
+int cgb_cg_history(cgb_ctx *ctx, cgb_csr *A, double *h_out, int64_t capacity, int64_t *count) {
+  CGB_REQUIRE(ctx && A && count, "cgb_cg_history: NULL argument");
+  *count = A->ws.hist_count;
+  if (!h_out || capacity <= 0 || A->ws.hist_count == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  const int64_t m = std::min<int64_t>(capacity, A->ws.hist_count);
+  CGB_CUDA(cudaMemcpyAsync(h_out, A->ws.hist, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,231 @@
+// cg_kernels.cuh — the kernels of one CG iteration (reference loop: src/CG.hpp:359-436).
+//
+//   K0  cg_init_kernel      r = b - A x0, rr = r.r                       (:314-341)
+//   K3  cg_pupdate_kernel   p = r + beta p     (only when not fused)      (:418)
+//   K1  cg_spmv_kernel      Ap = A p, pAp = p.Ap, alpha = rr / pAp        (:374-386)
+//       fused flavour: p = r + beta p_old is formed in the gather and written once
+//   K2  cg_update_kernel    x += alpha p, r -= alpha Ap, rr' = r.r,       (:390-416)
+//                           stop test on the OLD rr, beta = rr'/rr, rr = rr', ++iter
+//   K4  residual_kernel     sum (b - A x)^2, sum x^2                      (:477-499)
+//
+// Every kernel is gated on the device-side state (no host round trip per iteration): once the
+// stop test has fired or the trip cap is reached, later launches return immediately, so a CUDA
+// graph holding a batch of iterations can overshoot harmlessly.
+#pragma once
+#include "spmv.cuh"
+
+namespace cgb {
+
+struct CsrView {
+  int64_t n;
+  const int *rowptr;
+  const int *cols;
+  const double *vals;
+};
+
+__device__ __forceinline__ bool cg_active(const CgState *st) {
+  // reference: do { ... } while (counter++ < N && !*is_done)   (src/CG.hpp:436)
+  return !st->done && st->iter < st->max_iter;
+}
+
+// ---- K0 -------------------------------------------------------------------------------------
+template <int L>
+__global__ void __launch_bounds__(kBlock) cg_init_kernel(CsrView A, const double *__restrict__ x,
+                                                          const double *__restrict__ b, double *__restrict__ r,
+                                                          CgState *st, double *partials, double *hist) {
+  __shared__ double red[32];
+  double a0 = 0.0, a1 = 0.0;
+  GatherPlain g{x};
+  EpiInitResidual e{b, r};
+  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  a0 = block_sum(a0, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = a0;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rr = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      st->rr = rr;
+      st->rr0 = rr;
+      st->pAp = 0.0;
+      st->alpha = 0.0;
+      st->beta = 0.0; // first p-update yields p = r
+      st->iter = 0;
+      st->done = 0;
+      st->nan_stop = 0;
+      if (st->record_history && st->hist_cap > 0) hist[0] = rr;
+    }
+  }
+}
+
+// ---- K3 (unfused only) -------------------------------------------------------------------------
+static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, const double *__restrict__ r,
+                                                             double *__restrict__ p, const CgState *st) {
+  if (!cg_active(st)) return;
+  const double beta = st->beta;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  const double2 *r2 = reinterpret_cast<const double2 *>(r);
+  double2 *p2 = reinterpret_cast<double2 *>(p);
+  for (int64_t i = tid; i < n2; i += nthr) {
+    const double2 rv = r2[i];
+    double2 pv = p2[i];
+    pv.x = fma(beta, pv.x, rv.x);
+    pv.y = fma(beta, pv.y, rv.y);
+    p2[i] = pv;
+  }
+  if ((n & 1) && tid == 0) p[n - 1] = fma(beta, p[n - 1], r[n - 1]);
+}
+
+// ---- K1 -------------------------------------------------------------------------------------
+// FUSED: p buffers ping-pong on the iteration parity; p_old = pbuf[iter & 1], p_new = pbuf[~iter & 1].
+template <int L, bool FUSED>
+__global__ void __launch_bounds__(kBlock) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
+                                                          double *pbuf1, double *__restrict__ Ap, CgState *st,
+                                                          double *partials, double *local_out) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  double a0 = 0.0, a1 = 0.0;
+  if (FUSED) {
+    const bool odd = (st->iter & 1) != 0;
+    const double *p_old = odd ? pbuf1 : pbuf0;
+    double *p_new = odd ? pbuf0 : pbuf1;
+    const double beta = st->beta;
+    GatherFusedP g{r, p_old, beta};
+    EpiDotFusedP e{Ap, r, p_old, p_new, beta};
+    spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  } else {
+    GatherPlain g{pbuf0};
+    EpiDotP e{Ap, pbuf0};
+    spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  }
+  a0 = block_sum(a0, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = a0;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double pAp = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      if (local_out) {
+        *local_out = pAp; // multi-GPU: all-reduced before K2 forms alpha
+      } else {
+        st->pAp = pAp;
+        st->alpha = st->rr / pAp; // src/CG.hpp:385-386
+      }
+    }
+  }
+}
+
+// ---- K2 -------------------------------------------------------------------------------------
+// Single GPU (pAp_in == NULL, local_out == NULL): alpha comes from the state and the last CTA advances
+// the state.  Multi-GPU: alpha = rr / *pAp_in (the all-reduced p.Ap), the local r.r partial goes to
+// *local_out and cg_advance_kernel advances the state after the second all-reduce.
+template <bool FUSED>
+__global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__restrict__ x, const double *pbuf0,
+                                                            const double *pbuf1, double *__restrict__ r,
+                                                            const double *__restrict__ Ap, CgState *st,
+                                                            double *partials, double *hist,
+                                                            const double *pAp_in, double *local_out) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  const double alpha = pAp_in ? st->rr / *pAp_in : st->alpha;
+  // fused flavour: this iteration's p is the buffer K1 just wrote
+  const double *p = FUSED ? (((st->iter & 1) != 0) ? pbuf0 : pbuf1) : pbuf0;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  double2 *x2 = reinterpret_cast<double2 *>(x);
+  double2 *r2 = reinterpret_cast<double2 *>(r);
+  const double2 *p2 = reinterpret_cast<const double2 *>(p);
+  const double2 *q2 = reinterpret_cast<const double2 *>(Ap);
+  double acc = 0.0;
+  for (int64_t i = tid; i < n2; i += nthr) {
+    double2 xv = x2[i], rv = r2[i];
+    const double2 pv = p2[i], qv = q2[i];
+    xv.x = fma(alpha, pv.x, xv.x);
+    xv.y = fma(alpha, pv.y, xv.y);
+    rv.x = fma(-alpha, qv.x, rv.x);
+    rv.y = fma(-alpha, qv.y, rv.y);
+    x2[i] = xv;
+    r2[i] = rv;
+    acc = fma(rv.x, rv.x, acc);
+    acc = fma(rv.y, rv.y, acc);
+  }
+  if ((n & 1) && tid == 0) {
+    const int64_t i = n - 1;
+    x[i] = fma(alpha, p[i], x[i]);
+    const double rv = fma(-alpha, Ap[i], r[i]);
+    r[i] = rv;
+    acc = fma(rv, rv, acc);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rr_new = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      if (!local_out) {
+        const double rr = st->rr;
+        // stop test reads the rr from BEFORE this iteration's update (src/CG.hpp:396-404)
+        if (isnan(rr) || sqrt(rr) <= st->tol) {
+          st->done = 1;
+          if (isnan(rr)) st->nan_stop = 1;
+        }
+        st->beta = rr_new / rr; // :414
+        st->rr = rr_new;        // :415
+        const long long it = st->iter + 1;
+        st->iter = it;
+        if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
+      } else {
+        *local_out = rr_new;
+      }
+    }
+  }
+}
+
+// Multi-GPU: advance the state from the all-reduced scalars (one thread).
+static __global__ void cg_advance_kernel(CgState *st, const double *rr_global, double *hist) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (!cg_active(st)) return;
+  const double rr = st->rr, rr_new = *rr_global;
+  if (isnan(rr) || sqrt(rr) <= st->tol) {
+    st->done = 1;
+    if (isnan(rr)) st->nan_stop = 1;
+  }
+  st->beta = rr_new / rr;
+  st->rr = rr_new;
+  const long long it = st->iter + 1;
+  st->iter = it;
+  if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
+}
+
+// ---- K4 -------------------------------------------------------------------------------------
+template <int L>
+__global__ void __launch_bounds__(kBlock) residual_kernel(CsrView A, const double *__restrict__ x,
+                                                           const double *__restrict__ b, double *out2,
+                                                           double *partials, unsigned int *ticket) {
+  __shared__ double red[32];
+  double a0 = 0.0, a1 = 0.0;
+  GatherPlain g{x};
+  EpiAccuracy e{b, x};
+  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  a0 = block_sum(a0, red);
+  a1 = block_sum(a1, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = a0;
+    partials[kMaxPartials + blockIdx.x] = a1;
+  }
+  if (publish_and_elect(ticket, gridDim.x)) {
+    const double s0 = reduce_partials(partials, gridDim.x, red);
+    const double s1 = reduce_partials(partials + kMaxPartials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      out2[0] = s0;
+      out2[1] = s1;
+    }
+  }
+}
+
+// y = A x (plain)
+template <int L>
+__global__ void __launch_bounds__(kBlock) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
+  double a0 = 0.0, a1 = 0.0;
+  GatherPlain g{x};
+  EpiStore e{y};
+  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+}
+
+} // namespace cgb

@@ -1,0 +1,222 @@
+// core.cu — context, device memory, events, error reporting of the cgb200 C-ABI.
+// Interfaces replaced: acpp::sycl::queue / malloc_device / free / copy / fill / event as used by
+// the reference in src/LinearAlgebraTypes.hpp:43-49,101-121,160-183,213-224 and src/CG.hpp:561-578.
+#include "common.cuh"
+
+#include <stdarg.h>
+
+namespace cgb {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int ctx_scratch(cgb_ctx *ctx) {
+  if (ctx->partials) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMalloc(&ctx->partials, sizeof(double) * 2 * kMaxPartials));
+  CGB_CUDA(cudaMalloc(&ctx->ticket, sizeof(unsigned int) * 4));
+  CGB_CUDA(cudaMemsetAsync(ctx->ticket, 0, sizeof(unsigned int) * 4, ctx->stream));
+  return CGB_OK;
+}
+
+} // namespace cgb
+
+using namespace cgb;
+
+extern "C" {
+
+const char *cgb_last_error(void) { return g_err; }
+int cgb_version(void) { return CGB_VERSION; }
+
+int cgb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int cgb_ctx_create(int device, cgb_ctx **out) {
+  CGB_REQUIRE(out != nullptr, "cgb_ctx_create: out is NULL");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return fail(CGB_ERR_CUDA, "cgb_ctx_create: no CUDA device available (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= count) return fail(CGB_ERR_INVALID, "cgb_ctx_create: device %d out of range [0,%d)", device, count);
+  cudaDeviceProp prop;
+  CGB_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(CGB_ERR_CUDA, "cgb_ctx_create: device %d is sm_%d%d; this library ships sm_100a code only", device,
+                prop.major, prop.minor);
+  ScopedDevice sd(device);
+  cgb_ctx *ctx = new cgb_ctx();
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->coop_ok = prop.cooperativeLaunch;
+  ctx->l2_bytes = (size_t)prop.l2CacheSize;
+  ctx->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
+  e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    delete ctx;
+    return fail(CGB_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+  }
+  e = cudaMallocHost(&ctx->pinned, 4096);
+  if (e != cudaSuccess) {
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return fail(CGB_ERR_CUDA, "cudaMallocHost failed: %s", cudaGetErrorString(e));
+  }
+  *out = ctx;
+  return CGB_OK;
+}
+
+int cgb_ctx_destroy(cgb_ctx *ctx) {
+  if (!ctx) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->partials) cudaFree(ctx->partials);
+  if (ctx->ticket) cudaFree(ctx->ticket);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return CGB_OK;
+}
+
+int cgb_ctx_sync(cgb_ctx *ctx) {
+  CGB_REQUIRE(ctx, "cgb_ctx_sync: ctx is NULL");
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+void *cgb_ctx_stream(cgb_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+int cgb_ctx_device(cgb_ctx *ctx) { return ctx ? ctx->device : -1; }
+int cgb_ctx_sm_count(cgb_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+
+int cgb_malloc(cgb_ctx *ctx, size_t bytes, void **d_out) {
+  CGB_REQUIRE(ctx && d_out, "cgb_malloc: NULL argument");
+  ScopedDevice sd(ctx->device);
+  *d_out = nullptr;
+  if (bytes == 0) bytes = 16; // cudaMalloc aligns to >= 256 bytes
+  CGB_CUDA(cudaMalloc(d_out, bytes));
+  return CGB_OK;
+}
+
+int cgb_free(cgb_ctx *ctx, void *d_ptr) {
+  if (!d_ptr) return CGB_OK;
+  CGB_REQUIRE(ctx, "cgb_free: ctx is NULL");
+  ScopedDevice sd(ctx->device);
+  // work queued on the stream may still use the buffer (reference: free after queue order)
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  CGB_CUDA(cudaFree(d_ptr));
+  return CGB_OK;
+}
+
+int cgb_memcpy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes, int sync) {
+  CGB_REQUIRE(ctx && (bytes == 0 || (d_dst && h_src)), "cgb_memcpy_h2d: NULL argument");
+  if (bytes == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+int cgb_memcpy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes, int sync) {
+  CGB_REQUIRE(ctx && (bytes == 0 || (h_dst && d_src)), "cgb_memcpy_d2h: NULL argument");
+  if (bytes == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+int cgb_memcpy_d2d(cgb_ctx *ctx, void *d_dst, const void *d_src, size_t bytes) {
+  CGB_REQUIRE(ctx && (bytes == 0 || (d_dst && d_src)), "cgb_memcpy_d2d: NULL argument");
+  if (bytes == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  return CGB_OK;
+}
+
+int cgb_memset(cgb_ctx *ctx, void *d_ptr, int byte, size_t bytes) {
+  CGB_REQUIRE(ctx && (bytes == 0 || d_ptr), "cgb_memset: NULL argument");
+  if (bytes == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMemsetAsync(d_ptr, byte, bytes, ctx->stream));
+  return CGB_OK;
+}
+
+int cgb_host_alloc(size_t bytes, void **h_out) {
+  CGB_REQUIRE(h_out, "cgb_host_alloc: out is NULL");
+  *h_out = nullptr;
+  CGB_CUDA(cudaMallocHost(h_out, bytes ? bytes : 16));
+  return CGB_OK;
+}
+
+int cgb_host_free(void *h_ptr) {
+  if (h_ptr) CGB_CUDA(cudaFreeHost(h_ptr));
+  return CGB_OK;
+}
+
+int cgb_event_record(cgb_ctx *ctx, cgb_event **out) {
+  CGB_REQUIRE(ctx && out, "cgb_event_record: NULL argument");
+  ScopedDevice sd(ctx->device);
+  cgb_event *ev = new cgb_event();
+  cudaError_t e = cudaEventCreate(&ev->ev);
+  if (e == cudaSuccess) e = cudaEventRecord(ev->ev, ctx->stream);
+  if (e != cudaSuccess) {
+    if (ev->ev) cudaEventDestroy(ev->ev);
+    delete ev;
+    *out = nullptr;
+    return fail(CGB_ERR_CUDA, "cgb_event_record: %s", cudaGetErrorString(e));
+  }
+  *out = ev;
+  return CGB_OK;
+}
+
+int cgb_event_sync(cgb_event *ev) {
+  CGB_REQUIRE(ev, "cgb_event_sync: event is NULL");
+  CGB_CUDA(cudaEventSynchronize(ev->ev));
+  return CGB_OK;
+}
+
+int cgb_event_elapsed_ms(cgb_event *start, cgb_event *stop, double *ms) {
+  CGB_REQUIRE(start && stop && ms, "cgb_event_elapsed_ms: NULL argument");
+  float f = 0.f;
+  CGB_CUDA(cudaEventSynchronize(stop->ev));
+  CGB_CUDA(cudaEventElapsedTime(&f, start->ev, stop->ev));
+  *ms = (double)f;
+  return CGB_OK;
+}
+
+int cgb_event_destroy(cgb_event *ev) {
+  if (!ev) return CGB_OK;
+  cudaEventDestroy(ev->ev);
+  delete ev;
+  return CGB_OK;
+}
+
+size_t cgb_memory_footprint(int64_t n, int64_t nnz) {
+  // reference formula, src/CG.hpp:555-558
+  return (size_t)(2 * nnz + 4 * n) * sizeof(double) + (size_t)(2 * n) * sizeof(int);
+}
+
+} // extern "C"

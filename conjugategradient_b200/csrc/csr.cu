@@ -1,0 +1,288 @@
+// csr.cu — device CSR handle, launch plan, plain SpMV, residual (accuracy) and the on-device
+// stencil generators.
+// Interfaces replaced: CGSolver::Matrix (reference src/LinearAlgebraTypes.hpp:57-132),
+// VectorOperations::spmv (src/VectorOperations.hpp:438-466), CG::accuracy (src/CG.hpp:463-515).
+#include "launch.cuh"
+
+#include <cub/device/device_scan.cuh>
+
+using namespace cgb;
+
+namespace cgb {
+
+int csr_plan(cgb_csr *A) {
+  const double mean = A->n > 0 ? (double)A->nnz / (double)A->n : 1.0;
+  int lanes = 2;
+  while (lanes < 32 && (double)lanes < mean) lanes <<= 1;
+  A->lanes = lanes;
+  const int sms = A->ctx->sm_count;
+  A->grid_spmv = sms * 8;
+  A->grid_vec = sms * 8;
+  // never launch more CTAs than there is work for
+  const int64_t rows_per_cta = (int64_t)(kBlock / lanes) * 2;
+  const int64_t need = (A->n + rows_per_cta - 1) / rows_per_cta;
+  if (need < A->grid_spmv) A->grid_spmv = (int)(need > 0 ? need : 1);
+  const int64_t need_v = (A->n / 2 + kBlock - 1) / kBlock;
+  if (need_v < A->grid_vec) A->grid_vec = (int)(need_v > 0 ? need_v : 1);
+  return CGB_OK;
+}
+
+void workspace_release(cgb_csr *A) {
+  Workspace &w = A->ws;
+  if (w.graph) cudaGraphExecDestroy(w.graph);
+  cudaFree(w.r);
+  cudaFree(w.p0);
+  cudaFree(w.p1);
+  cudaFree(w.Ap);
+  cudaFree(w.st);
+  cudaFree(w.partials);
+  cudaFree(w.hist);
+  if (w.h_st) cudaFreeHost(w.h_st);
+  for (auto &e : w.ev)
+    if (e) cudaEventDestroy(e);
+  w = Workspace();
+}
+
+int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap) {
+  Workspace &w = A->ws;
+  cgb_ctx *ctx = A->ctx;
+  if (w.n != A->n || w.n_ext != n_ext) {
+    workspace_release(A);
+    const size_t vb = sizeof(double) * (size_t)(n_ext > 0 ? n_ext : 1);
+    CGB_CUDA(cudaMalloc(&w.r, vb));
+    CGB_CUDA(cudaMalloc(&w.p0, vb));
+    CGB_CUDA(cudaMalloc(&w.Ap, vb));
+    CGB_CUDA(cudaMalloc(&w.st, sizeof(CgState)));
+    CGB_CUDA(cudaMalloc(&w.partials, sizeof(double) * 2 * kMaxPartials));
+    CGB_CUDA(cudaMallocHost(&w.h_st, 2 * sizeof(CgState)));
+    CGB_CUDA(cudaMemsetAsync(w.st, 0, sizeof(CgState), ctx->stream));
+    w.n = A->n;
+    w.n_ext = n_ext;
+  }
+  if (need_p1 && !w.p1) {
+    CGB_CUDA(cudaMalloc(&w.p1, sizeof(double) * (size_t)(n_ext > 0 ? n_ext : 1)));
+    if (w.graph) {
+      cudaGraphExecDestroy(w.graph);
+      w.graph = nullptr;
+    }
+  }
+  if (hist_cap > w.hist_cap) {
+    cudaFree(w.hist);
+    w.hist = nullptr;
+    CGB_CUDA(cudaMalloc(&w.hist, sizeof(double) * (size_t)hist_cap));
+    w.hist_cap = hist_cap;
+    if (w.graph) {
+      cudaGraphExecDestroy(w.graph);
+      w.graph = nullptr;
+    }
+  }
+  return CGB_OK;
+}
+
+// ---- stencil generation -----------------------------------------------------------------------
+// kind 0: 2D 5-point (diag 4), 1: 3D 7-point (diag 6), 2: 3D 27-point (diag 26); neighbours -1;
+// natural ordering row = i + m*j + m*m*k; Dirichlet truncation at the boundary.
+__device__ __forceinline__ int stencil_row_len(int kind, int64_t m, int64_t mz, int64_t row) {
+  const int64_t i = row % m, j = (row / m) % m, k = row / (m * m);
+  const int nx = 1 + (i > 0) + (i < m - 1), ny = 1 + (j > 0) + (j < m - 1);
+  if (kind == 0) return 1 + (nx - 1) + (ny - 1);
+  const int nz = 1 + (k > 0) + (k < mz - 1);
+  if (kind == 1) return 1 + (nx - 1) + (ny - 1) + (nz - 1);
+  return nx * ny * nz;
+}
+
+__global__ void stencil_len_kernel(int kind, int64_t m, int64_t mz, int64_t row_begin, int64_t nloc, int *len) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < nloc) len[t] = stencil_row_len(kind, m, mz, row_begin + t);
+}
+
+__global__ void stencil_fill_kernel(int kind, int64_t m, int64_t mz, int64_t row_begin, int64_t nloc,
+                                    const int *__restrict__ rowptr, int *__restrict__ cols,
+                                    double *__restrict__ vals) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nloc) return;
+  const int64_t row = row_begin + t;
+  const int64_t i = row % m, j = (row / m) % m, k = row / (m * m);
+  int64_t o = rowptr[t];
+  if (kind == 2) {
+    for (int dz = -1; dz <= 1; dz++) {
+      if (k + dz < 0 || k + dz >= mz) continue;
+      for (int dy = -1; dy <= 1; dy++) {
+        if (j + dy < 0 || j + dy >= m) continue;
+        for (int dx = -1; dx <= 1; dx++) {
+          if (i + dx < 0 || i + dx >= m) continue;
+          const int64_t c = row + dx + dy * m + dz * m * m;
+          cols[o] = (int)c;
+          vals[o] = (c == row) ? 26.0 : -1.0;
+          o++;
+        }
+      }
+    }
+    return;
+  }
+  const double diag = kind == 0 ? 4.0 : 6.0;
+  if (kind == 1 && k > 0) { cols[o] = (int)(row - m * m); vals[o++] = -1.0; }
+  if (j > 0) { cols[o] = (int)(row - m); vals[o++] = -1.0; }
+  if (i > 0) { cols[o] = (int)(row - 1); vals[o++] = -1.0; }
+  cols[o] = (int)row; vals[o++] = diag;
+  if (i < m - 1) { cols[o] = (int)(row + 1); vals[o++] = -1.0; }
+  if (j < m - 1) { cols[o] = (int)(row + m); vals[o++] = -1.0; }
+  if (kind == 1 && k < mz - 1) { cols[o] = (int)(row + m * m); vals[o++] = -1.0; }
+}
+
+} // namespace cgb
+
+extern "C" {
+
+int cgb_csr_from_device(cgb_ctx *ctx, int64_t n, int64_t nnz, double *d_vals, int32_t *d_cols, int32_t *d_rowptr,
+                        int take_ownership, cgb_csr **out) {
+  CGB_REQUIRE(ctx && out, "cgb_csr_from_device: NULL argument");
+  CGB_REQUIRE(n >= 0 && nnz >= 0 && nnz < ((int64_t)1 << 31) && n < ((int64_t)1 << 31),
+              "cgb_csr: n and nnz must fit the reference's 32-bit indices");
+  CGB_REQUIRE(d_rowptr && (nnz == 0 || (d_vals && d_cols)), "cgb_csr_from_device: NULL array");
+  cgb_csr *A = new cgb_csr();
+  A->ctx = ctx;
+  A->n = n;
+  A->nnz = nnz;
+  A->n_cols = n;
+  A->vals = d_vals;
+  A->cols = d_cols;
+  A->rowptr = d_rowptr;
+  A->owns = take_ownership != 0;
+  csr_plan(A);
+  *out = A;
+  return CGB_OK;
+}
+
+int cgb_csr_create(cgb_ctx *ctx, int64_t n, int64_t nnz, const double *h_vals, const int32_t *h_cols,
+                   const int32_t *h_rowptr, cgb_csr **out) {
+  CGB_REQUIRE(ctx && out, "cgb_csr_create: NULL argument");
+  CGB_REQUIRE(h_rowptr && (nnz == 0 || (h_vals && h_cols)), "cgb_csr_create: NULL array");
+  CGB_REQUIRE(n >= 0 && nnz >= 0 && nnz < ((int64_t)1 << 31) && n < ((int64_t)1 << 31),
+              "cgb_csr: n and nnz must fit the reference's 32-bit indices");
+  ScopedDevice sd(ctx->device);
+  double *dv = nullptr;
+  int32_t *dc = nullptr, *dr = nullptr;
+  // +16 bytes of slack so 128-bit loads that start inside the array never leave the allocation
+  cudaError_t e = cudaMalloc(&dv, sizeof(double) * (size_t)nnz + 64);
+  if (e == cudaSuccess) e = cudaMalloc(&dc, sizeof(int32_t) * (size_t)nnz + 64);
+  if (e == cudaSuccess) e = cudaMalloc(&dr, sizeof(int32_t) * (size_t)(n + 1) + 64);
+  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(dv, h_vals, sizeof(double) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(dc, h_cols, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(dr, h_rowptr, sizeof(int32_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, ctx->stream);
+  // the host arrays are only borrowed until this call returns (reference waits in setTarget, src/CG.hpp:169)
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    cudaFree(dv);
+    cudaFree(dc);
+    cudaFree(dr);
+    return fail(CGB_ERR_CUDA, "cgb_csr_create: %s", cudaGetErrorString(e));
+  }
+  return cgb_csr_from_device(ctx, n, nnz, dv, dc, dr, 1, out);
+}
+
+int cgb_csr_destroy(cgb_csr *A) {
+  if (!A) return CGB_OK;
+  ScopedDevice sd(A->ctx->device);
+  cudaStreamSynchronize(A->ctx->stream);
+  workspace_release(A);
+  cudaFree(A->sell_vals);
+  cudaFree(A->sell_cols);
+  cudaFree(A->sell_off);
+  cudaFree(A->sell_perm);
+  if (A->owns) {
+    cudaFree(A->vals);
+    cudaFree(A->cols);
+    cudaFree(A->rowptr);
+  }
+  delete A;
+  return CGB_OK;
+}
+
+int64_t cgb_csr_n(const cgb_csr *A) { return A ? A->n : 0; }
+int64_t cgb_csr_nnz(const cgb_csr *A) { return A ? A->nnz : 0; }
+double *cgb_csr_vals(cgb_csr *A) { return A ? A->vals : nullptr; }
+int32_t *cgb_csr_cols(cgb_csr *A) { return A ? A->cols : nullptr; }
+int32_t *cgb_csr_rowptr(cgb_csr *A) { return A ? A->rowptr : nullptr; }
+
+int cgb_csr_set_format(cgb_csr *A, int format) {
+  CGB_REQUIRE(A, "cgb_csr_set_format: NULL matrix");
+  CGB_REQUIRE(format == CGB_FMT_AUTO || format == CGB_FMT_CSR || format == CGB_FMT_SELL, "unknown format");
+  A->format = format;
+  return CGB_OK;
+}
+int cgb_csr_get_format(const cgb_csr *A) { return A ? A->format : 0; }
+
+int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
+  CGB_REQUIRE(ctx && A && d_x && d_y, "cgb_spmv: NULL argument");
+  if (A->n == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  CGB_LAUNCH_L(A->lanes, spmv_kernel, A->grid_spmv, ctx->stream, V, d_x, d_y);
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
+int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b, double *rr, double *xx) {
+  CGB_REQUIRE(ctx && A && d_x && d_b && rr && xx, "cgb_residual: NULL argument");
+  ScopedDevice sd(ctx->device);
+  CGB_TRY(ctx_scratch(ctx));
+  if (A->n == 0) {
+    *rr = 0.0;
+    *xx = 0.0;
+    return CGB_OK;
+  }
+  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  double *out2 = ctx->partials + 2 * kMaxPartials - 2; // tail of the scratch is never a partial slot
+  CGB_LAUNCH_L(A->lanes, residual_kernel, A->grid_spmv, ctx->stream, V, d_x, d_b, out2, ctx->partials, ctx->ticket);
+  CGB_CUDA(cudaGetLastError());
+  CGB_CUDA(cudaMemcpyAsync(ctx->pinned, out2, 2 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  *rr = ctx->pinned[0];
+  *xx = ctx->pinned[1];
+  return CGB_OK;
+}
+
+int cgb_gen_stencil(cgb_ctx *ctx, int kind, int64_t m, int64_t mz, int64_t row_begin, int64_t row_end, cgb_csr **out) {
+  CGB_REQUIRE(ctx && out, "cgb_gen_stencil: NULL argument");
+  CGB_REQUIRE(kind >= 0 && kind <= 2 && m >= 1, "cgb_gen_stencil: bad kind or size");
+  if (kind == 0) mz = 1;
+  if (mz <= 0) mz = m;
+  const int64_t n = m * m * mz;
+  if (row_end < 0) row_end = n;
+  CGB_REQUIRE(row_begin >= 0 && row_begin <= row_end && row_end <= n, "cgb_gen_stencil: bad row range");
+  CGB_REQUIRE(n < ((int64_t)1 << 31), "cgb_gen_stencil: n must fit 32-bit column indices");
+  ScopedDevice sd(ctx->device);
+  const int64_t nloc = row_end - row_begin;
+  int32_t *rowptr = nullptr, *cols = nullptr;
+  double *vals = nullptr;
+  CGB_CUDA(cudaMalloc(&rowptr, sizeof(int32_t) * (size_t)(nloc + 1) + 64));
+  CGB_CUDA(cudaMemsetAsync(rowptr, 0, sizeof(int32_t), ctx->stream));
+  const int tb = 256;
+  const unsigned gb = (unsigned)((nloc + tb - 1) / tb);
+  int64_t nnz = 0;
+  if (nloc > 0) {
+    stencil_len_kernel<<<gb, tb, 0, ctx->stream>>>(kind, m, mz, row_begin, nloc, rowptr + 1);
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, rowptr + 1, rowptr + 1, (int)nloc, ctx->stream);
+    void *tmp = nullptr;
+    CGB_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, rowptr + 1, rowptr + 1, (int)nloc, ctx->stream);
+    int last = 0;
+    CGB_CUDA(cudaMemcpyAsync(&last, rowptr + nloc, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(tmp);
+    nnz = last;
+  }
+  CGB_CUDA(cudaMalloc(&cols, sizeof(int32_t) * (size_t)nnz + 64));
+  CGB_CUDA(cudaMalloc(&vals, sizeof(double) * (size_t)nnz + 64));
+  if (nloc > 0) {
+    stencil_fill_kernel<<<gb, tb, 0, ctx->stream>>>(kind, m, mz, row_begin, nloc, rowptr, cols, vals);
+    CGB_CUDA(cudaGetLastError());
+  }
+  int rc = cgb_csr_from_device(ctx, nloc, nnz, vals, cols, rowptr, 1, out);
+  if (rc == CGB_OK) (*out)->n_cols = n;
+  return rc;
+}
+
+} // extern "C"

@@ -1,0 +1,395 @@
+// dist.cu — row-partitioned multi-GPU CG (new: the reference is single-device).
+//
+// One process per GPU.  Rank r owns global rows [row_starts[r], row_starts[r+1]).  Its row block
+// is split once, on the device, into
+//   A_loc  : all local rows, only the columns it owns (indices rebased to the block), and
+//   A_halo : only the rows that touch remote columns, indices into a compact halo buffer.
+// Per iteration:  p-update -> pack boundary entries of p -> NCCL send/recv on a side stream,
+// overlapped with the A_loc SpMV -> A_halo correction -> all-reduce p.Ap -> x/r update ->
+// all-reduce r.r -> state advance.  NCCL is resolved with dlopen so single-GPU users never need it.
+#include "launch.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <vector>
+
+using namespace cgb;
+
+// ---- NCCL through dlopen ------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int nccl_load() {
+  if (g_nccl.handle) return CGB_OK;
+  void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return fail(CGB_ERR_NCCL, "cannot load libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                        \
+  *(void **)(&g_nccl.field) = dlsym(h, name);                                   \
+  if (!g_nccl.field) return fail(CGB_ERR_NCCL, "libnccl lacks symbol %s", name)
+  SYM(GetUniqueId, "ncclGetUniqueId");
+  SYM(CommInitRank, "ncclCommInitRank");
+  SYM(CommDestroy, "ncclCommDestroy");
+  SYM(AllReduce, "ncclAllReduce");
+  SYM(AllGather, "ncclAllGather");
+  SYM(Send, "ncclSend");
+  SYM(Recv, "ncclRecv");
+  SYM(GroupStart, "ncclGroupStart");
+  SYM(GroupEnd, "ncclGroupEnd");
+  SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+  g_nccl.handle = h;
+  return CGB_OK;
+}
+
+#define CGB_NCCL(expr)                                                                                   \
+  do {                                                                                                   \
+    ncclResult_t _r = (expr);                                                                            \
+    if (_r != ncclSuccess)                                                                               \
+      return fail(CGB_ERR_NCCL, "%s failed: %s (%s:%d)", #expr, g_nccl.GetErrorString(_r), __FILE__, __LINE__); \
+  } while (0)
+} // namespace
+
+struct cgb_dist {
+  cgb_ctx *ctx = nullptr;
+  int rank = 0, nranks = 1;
+  ncclComm_t comm = nullptr;
+  std::vector<int64_t> row_starts;
+  int64_t n = 0;        // local rows
+  cgb_csr *Aloc = nullptr;
+  cgb_csr *Ahalo = nullptr;   // nh rows, columns index the halo buffer
+  int32_t *halo_rows = nullptr; // nh local row ids
+  int64_t nh = 0;
+  int64_t H = 0;              // halo entries received
+  int64_t S = 0;              // entries sent
+  std::vector<int64_t> rcount, roff, scount, soff;
+  int32_t *send_idx = nullptr; // local indices to pack, grouped by destination rank
+  double *send_buf = nullptr;
+  double *halo = nullptr;
+  double *scal = nullptr;      // [0] pAp local, [1] pAp global, [2] rr local, [3] rr global, [4..5] residual
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_pack = nullptr, ev_halo = nullptr;
+};
+
+namespace {
+
+// ---- setup kernels (one-off) ----------------------------------------------------------------------
+__global__ void count_split_kernel(int64_t n, const int *rowptr, const int *cols, int lo, int hi, int *cnt_loc,
+                                   int *cnt_rem) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int l = 0, r = 0;
+  for (int j = rowptr[i]; j < rowptr[i + 1]; j++) {
+    const int c = cols[j];
+    if (c >= lo && c < hi) l++; else r++;
+  }
+  cnt_loc[i] = l;
+  cnt_rem[i] = r;
+}
+
+struct IsRemote {
+  int lo, hi;
+  __host__ __device__ bool operator()(const int &c) const { return c < lo || c >= hi; }
+};
+struct NonZero {
+  __host__ __device__ bool operator()(const int &c) const { return c != 0; }
+};
+
+__device__ __forceinline__ int lower_bound_dev(const int *a, int n, int key) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (a[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// halo_slot[i] = index of row i among the rows that have remote entries (valid where cnt_rem[i] > 0)
+__global__ void split_fill_kernel(int64_t n, const int *rowptr, const int *cols, const double *vals, int lo, int hi,
+                                  const int *rowptr_loc, int *cols_loc, double *vals_loc, const int *cnt_rem,
+                                  const int *halo_slot, const int *rowptr_halo, int *cols_halo, double *vals_halo,
+                                  int *halo_rows, const int *recv_cols, int H) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int ol = rowptr_loc[i];
+  int oh = 0;
+  const bool has = cnt_rem[i] > 0;
+  if (has) {
+    const int slot = halo_slot[i];
+    oh = rowptr_halo[slot];
+    halo_rows[slot] = (int)i;
+  }
+  for (int j = rowptr[i]; j < rowptr[i + 1]; j++) {
+    const int c = cols[j];
+    if (c >= lo && c < hi) {
+      cols_loc[ol] = c - lo;
+      vals_loc[ol++] = vals[j];
+    } else {
+      cols_halo[oh] = lower_bound_dev(recv_cols, H, c);
+      vals_halo[oh++] = vals[j];
+    }
+  }
+}
+
+__global__ void rebase_kernel(int *idx, int64_t n, int lo) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) idx[i] -= lo;
+}
+
+// ---- per-iteration kernels ------------------------------------------------------------------------
+__global__ void pack_kernel(int64_t S, const int *__restrict__ send_idx, const double *__restrict__ p,
+                            double *__restrict__ send_buf, const CgState *st, int gated) {
+  if (gated && !cg_active(st)) return;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = tid; k < S; k += nthr) send_buf[k] = p[send_idx[k]];
+}
+
+// y[halo_rows[k]] += sum_j vals[j] * halo[cols[j]]; optionally the p.Ap correction:
+// out[0] = base[0] + sum_k p[row] * (halo part of row).  One CTA (the halo part is tiny).
+__global__ void __launch_bounds__(kBlock) halo_spmv_kernel(int64_t nh, const int *__restrict__ rowptr,
+                                                            const int *__restrict__ cols,
+                                                            const double *__restrict__ vals,
+                                                            const int *__restrict__ halo_rows,
+                                                            const double *__restrict__ halo, double *y,
+                                                            const double *p, const double *base, double *out,
+                                                            const CgState *st, int gated, double sign) {
+  if (gated && !cg_active(st)) return;
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (int64_t k = threadIdx.x; k < nh; k += blockDim.x) {
+    double s = 0.0;
+    for (int j = rowptr[k]; j < rowptr[k + 1]; j++) s = fma(vals[j], halo[cols[j]], s);
+    const int row = halo_rows[k];
+    y[row] += sign * s;
+    if (p) acc = fma(p[row], s, acc);
+  }
+  if (out) {
+    acc = block_sum(acc, red);
+    if (threadIdx.x == 0) out[0] = (base ? base[0] : 0.0) + acc;
+  }
+}
+
+// Multi-CTA flavour for large halos: partial sums per CTA, last CTA finalises.
+__global__ void __launch_bounds__(kBlock) halo_spmv_multi_kernel(int64_t nh, const int *__restrict__ rowptr,
+                                                                  const int *__restrict__ cols,
+                                                                  const double *__restrict__ vals,
+                                                                  const int *__restrict__ halo_rows,
+                                                                  const double *__restrict__ halo, double *y,
+                                                                  const double *p, const double *base, double *out,
+                                                                  CgState *st, int gated, double *partials) {
+  if (gated && !cg_active(st)) return;
+  __shared__ double red[32];
+  double acc = 0.0;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = tid; k < nh; k += nthr) {
+    double s = 0.0;
+    for (int j = rowptr[k]; j < rowptr[k + 1]; j++) s = fma(vals[j], halo[cols[j]], s);
+    const int row = halo_rows[k];
+    y[row] += s;
+    if (p) acc = fma(p[row], s, acc);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double s = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0 && out) out[0] = (base ? base[0] : 0.0) + s;
+  }
+}
+
+// r = b - t, partial r.r -> *local_out            (dist flavour of K0, src/CG.hpp:324-341)
+__global__ void __launch_bounds__(kBlock) dist_init_kernel(int64_t n, const double *__restrict__ b,
+                                                            const double *__restrict__ t, double *__restrict__ r,
+                                                            CgState *st, double *partials, double *local_out) {
+  __shared__ double red[32];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double acc = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double ri = b[i] - t[i];
+    r[i] = ri;
+    acc = fma(ri, ri, acc);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double s = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) *local_out = s;
+  }
+}
+
+__global__ void dist_arm_kernel(CgState *st, const double *rr_global, double *hist) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const double rr = *rr_global;
+  st->rr = rr;
+  st->rr0 = rr;
+  st->pAp = 0.0;
+  st->alpha = 0.0;
+  st->beta = 0.0;
+  st->iter = 0;
+  st->done = 0;
+  st->nan_stop = 0;
+  if (st->record_history && st->hist_cap > 0) hist[0] = rr;
+}
+
+// sum (b - t)^2 and sum x^2 -> out[0], out[1] (local)        (src/CG.hpp:487-498)
+__global__ void __launch_bounds__(kBlock) dist_resid_kernel(int64_t n, const double *__restrict__ b,
+                                                             const double *__restrict__ t,
+                                                             const double *__restrict__ x, CgState *st,
+                                                             double *partials, double *out) {
+  __shared__ double red[32];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double a0 = 0.0, a1 = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double a = b[i] - t[i];
+    a0 = fma(a, a, a0);
+    a1 = fma(x[i], x[i], a1);
+  }
+  a0 = block_sum(a0, red);
+  a1 = block_sum(a1, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = a0;
+    partials[kMaxPartials + blockIdx.x] = a1;
+  }
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double s0 = reduce_partials(partials, gridDim.x, red);
+    const double s1 = reduce_partials(partials + kMaxPartials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      out[0] = s0;
+      out[1] = s1;
+    }
+  }
+}
+
+template <class T>
+int d2h_vec(cgb_ctx *ctx, std::vector<T> &out, const T *d, size_t n) {
+  out.resize(n);
+  if (n) CGB_CUDA(cudaMemcpyAsync(out.data(), d, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+int owner_of(const std::vector<int64_t> &rs, int64_t col) {
+  return (int)(std::upper_bound(rs.begin(), rs.end(), col) - rs.begin()) - 1;
+}
+
+// Exchange p's boundary entries: pack on the main stream, send/recv on the comm stream.
+// On return the comm stream has ev_halo recorded; the caller makes the main stream wait for it.
+int halo_exchange(cgb_dist *d, const double *vec, int gated) {
+  cudaStream_t s = d->ctx->stream, c = d->comm_stream;
+  if (d->S > 0) {
+    const int grid = (int)std::min<int64_t>((d->S + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 2);
+    pack_kernel<<<grid, kBlock, 0, s>>>(d->S, d->send_idx, vec, d->send_buf, d->Aloc->ws.st, gated);
+    CGB_CUDA(cudaGetLastError());
+  }
+  CGB_CUDA(cudaEventRecord(d->ev_pack, s));
+  CGB_CUDA(cudaStreamWaitEvent(c, d->ev_pack, 0));
+  CGB_NCCL(g_nccl.GroupStart());
+  for (int q = 0; q < d->nranks; q++) {
+    if (d->scount[q] > 0) CGB_NCCL(g_nccl.Send(d->send_buf + d->soff[q], (size_t)d->scount[q], ncclDouble, q, d->comm, c));
+    if (d->rcount[q] > 0) CGB_NCCL(g_nccl.Recv(d->halo + d->roff[q], (size_t)d->rcount[q], ncclDouble, q, d->comm, c));
+  }
+  CGB_NCCL(g_nccl.GroupEnd());
+  CGB_CUDA(cudaEventRecord(d->ev_halo, c));
+  return CGB_OK;
+}
+
+int halo_apply(cgb_dist *d, double *y, const double *p, const double *base, double *out, int gated) {
+  cudaStream_t s = d->ctx->stream;
+  CGB_CUDA(cudaStreamWaitEvent(s, d->ev_halo, 0));
+  Workspace &w = d->Aloc->ws;
+  if (d->nh > 64 * kBlock) {
+    const int grid = (int)std::min<int64_t>((d->nh + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 4);
+    halo_spmv_multi_kernel<<<grid, kBlock, 0, s>>>(d->nh, d->Ahalo->rowptr, d->Ahalo->cols, d->Ahalo->vals,
+                                                   d->halo_rows, d->halo, y, p, base, out, w.st, gated, w.partials);
+  } else {
+    halo_spmv_kernel<<<1, kBlock, 0, s>>>(d->nh, d->Ahalo ? d->Ahalo->rowptr : nullptr,
+                                          d->Ahalo ? d->Ahalo->cols : nullptr, d->Ahalo ? d->Ahalo->vals : nullptr,
+                                          d->halo_rows, d->halo, y, p, base, out, w.st, gated, 1.0);
+  }
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int cgb_nccl_unique_id(void *h_id128) {
+  CGB_REQUIRE(h_id128, "cgb_nccl_unique_id: NULL argument");
+  CGB_TRY(nccl_load());
+  ncclUniqueId id;
+  CGB_NCCL(g_nccl.GetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == CGB_NCCL_ID_BYTES, "ncclUniqueId size");
+  memcpy(h_id128, &id, sizeof(id));
+  return CGB_OK;
+}
+
+int cgb_plan_halo(int rank, int nranks, const int64_t *row_starts, int64_t nnz_local, const int32_t *h_cols,
+                  int32_t *h_recv_cols, int64_t capacity, int64_t *recv_count, int64_t *recv_per_rank) {
+  CGB_REQUIRE(row_starts && recv_count && nranks >= 1 && rank >= 0 && rank < nranks && (nnz_local == 0 || h_cols),
+              "cgb_plan_halo: bad argument");
+  const int64_t lo = row_starts[rank], hi = row_starts[rank + 1];
+  std::vector<int32_t> rem;
+  for (int64_t j = 0; j < nnz_local; j++)
+    if (h_cols[j] < lo || h_cols[j] >= hi) rem.push_back(h_cols[j]);
+  std::sort(rem.begin(), rem.end());
+  rem.erase(std::unique(rem.begin(), rem.end()), rem.end());
+  *recv_count = (int64_t)rem.size();
+  if (recv_per_rank) {
+    std::vector<int64_t> rs(row_starts, row_starts + nranks + 1);
+    for (int q = 0; q < nranks; q++) recv_per_rank[q] = 0;
+    for (int32_t c : rem) {
+      const int q = owner_of(rs, c);
+      if (q < 0 || q >= nranks) return fail(CGB_ERR_INVALID, "cgb_plan_halo: column %d outside the global range", c);
+      recv_per_rank[q]++;
+    }
+  }
+  if (h_recv_cols) {
+    CGB_REQUIRE(capacity >= (int64_t)rem.size(), "cgb_plan_halo: capacity too small");
+    std::copy(rem.begin(), rem.end(), h_recv_cols);
+  }
+  return CGB_OK;
+}
+
+int cgb_dist_destroy(cgb_dist *d) {
+  if (!d) return CGB_OK;
+  ScopedDevice sd(d->ctx->device);
+  cudaStreamSynchronize(d->ctx->stream);
+  if (d->comm_stream) cudaStreamSynchronize(d->comm_stream);
+  if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
+  cgb_csr_destroy(d->Aloc);
+  cgb_csr_destroy(d->Ahalo);
+  cudaFree(d->halo_rows);
+  cudaFree(d->send_idx);
+  cudaFree(d->send_buf);
+  cudaFree(d->halo);
+  cudaFree(d->scal);
+  if (d->ev_pack) cudaEventDestroy(d->ev_pack);
+  if (d->ev_halo) cudaEventDestroy(d->ev_halo);
+  if (d->comm_stream) cudaStreamDestroy(d->comm_stream);
+  delete d;
+  return CGB_OK;
+}
+
+int64_t cgb_dist_halo_count(const cgb_dist *d) { return d ? d->H : 0; }
+
+} // extern "C"
+
+#include "dist_impl.cuh"

@@ -1,0 +1,371 @@
+// dist_impl.cuh — second half of dist.cu: set-up (matrix split + halo plan) and the solve loop.
+#pragma once
+
+namespace {
+
+__global__ void flag_kernel(int64_t n, const int *cnt, int *flag) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flag[i] = cnt[i] > 0;
+}
+
+struct DevBuf { // frees on scope exit
+  void *p = nullptr;
+  ~DevBuf() { cudaFree(p); }
+  template <class T> T *as() { return (T *)p; }
+};
+
+int dev_alloc(DevBuf &b, size_t bytes) {
+  CGB_CUDA(cudaMalloc(&b.p, bytes ? bytes : 16));
+  return CGB_OK;
+}
+
+int read_int(cgb_ctx *ctx, const int *d, int *out) {
+  CGB_CUDA(cudaMemcpyAsync(out, d, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
+int dist_setup(cgb_dist *d, cgb_csr *A) {
+  cgb_ctx *ctx = d->ctx;
+  cudaStream_t s = ctx->stream;
+  const int64_t n = A->n;
+  const int lo = (int)d->row_starts[d->rank], hi = (int)d->row_starts[d->rank + 1];
+  const int tb = 256;
+  const unsigned gb = (unsigned)std::max<int64_t>(1, (n + tb - 1) / tb);
+  DevBuf b_cl, b_cr, b_flag, b_slot, b_tmp, b_rem, b_rem_sorted, b_num, b_cnt_compact;
+  CGB_TRY(dev_alloc(b_cl, sizeof(int) * (size_t)(n + 1)));
+  CGB_TRY(dev_alloc(b_cr, sizeof(int) * (size_t)(n + 1)));
+  CGB_TRY(dev_alloc(b_flag, sizeof(int) * (size_t)(n + 1)));
+  CGB_TRY(dev_alloc(b_slot, sizeof(int) * (size_t)(n + 1)));
+  CGB_TRY(dev_alloc(b_num, sizeof(int) * 4));
+  int *cnt_loc = b_cl.as<int>(), *cnt_rem = b_cr.as<int>(), *flag = b_flag.as<int>(), *slot = b_slot.as<int>();
+  int *d_num = b_num.as<int>();
+  if (n > 0) {
+    count_split_kernel<<<gb, tb, 0, s>>>(n, A->rowptr, A->cols, lo, hi, cnt_loc, cnt_rem);
+    flag_kernel<<<gb, tb, 0, s>>>(n, cnt_rem, flag);
+    CGB_CUDA(cudaGetLastError());
+  }
+  // temp storage big enough for every cub call below
+  size_t tmp_bytes = 0, t;
+  const int ni = (int)n, nz = (int)A->nnz;
+  int *nullp = nullptr;
+  cub::DeviceScan::InclusiveSum(nullptr, t, nullp, nullp, ni, s); tmp_bytes = std::max(tmp_bytes, t);
+  cub::DeviceScan::ExclusiveSum(nullptr, t, nullp, nullp, ni, s); tmp_bytes = std::max(tmp_bytes, t);
+  cub::DeviceSelect::If(nullptr, t, nullp, nullp, nullp, nz, IsRemote{lo, hi}, s); tmp_bytes = std::max(tmp_bytes, t);
+  cub::DeviceSelect::If(nullptr, t, nullp, nullp, nullp, ni, NonZero{}, s); tmp_bytes = std::max(tmp_bytes, t);
+  CGB_TRY(dev_alloc(b_tmp, tmp_bytes));
+
+  // A_loc row offsets
+  int32_t *rowptr_loc = nullptr;
+  CGB_CUDA(cudaMalloc(&rowptr_loc, sizeof(int32_t) * (size_t)(n + 1) + 64));
+  CGB_CUDA(cudaMemsetAsync(rowptr_loc, 0, sizeof(int32_t), s));
+  int nnz_loc = 0, nh = 0, nnz_halo = 0;
+  if (n > 0) {
+    t = tmp_bytes;
+    cub::DeviceScan::InclusiveSum(b_tmp.p, t, cnt_loc, rowptr_loc + 1, ni, s);
+    CGB_TRY(read_int(ctx, rowptr_loc + n, &nnz_loc));
+    t = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(b_tmp.p, t, flag, slot, ni, s);
+    int last_slot = 0, last_flag = 0;
+    CGB_TRY(read_int(ctx, slot + n - 1, &last_slot));
+    CGB_TRY(read_int(ctx, flag + n - 1, &last_flag));
+    nh = last_slot + last_flag;
+  }
+  nnz_halo = (int)A->nnz - nnz_loc;
+  d->nh = nh;
+
+  // A_halo row offsets: compact the non-zero remote counts (row order), then scan
+  int32_t *rowptr_halo = nullptr;
+  CGB_CUDA(cudaMalloc(&rowptr_halo, sizeof(int32_t) * (size_t)(nh + 1) + 64));
+  CGB_CUDA(cudaMemsetAsync(rowptr_halo, 0, sizeof(int32_t), s));
+  if (nh > 0) {
+    t = tmp_bytes;
+    cub::DeviceSelect::If(b_tmp.p, t, cnt_rem, rowptr_halo + 1, d_num, ni, NonZero{}, s);
+    t = tmp_bytes;
+    cub::DeviceScan::InclusiveSum(b_tmp.p, t, rowptr_halo + 1, rowptr_halo + 1, nh, s);
+  }
+
+  // receive list: sorted distinct remote columns
+  CGB_TRY(dev_alloc(b_rem, sizeof(int) * (size_t)(nnz_halo + 1)));
+  CGB_TRY(dev_alloc(b_rem_sorted, sizeof(int) * (size_t)(nnz_halo + 1)));
+  int32_t *recv_cols = nullptr;
+  CGB_CUDA(cudaMalloc(&recv_cols, sizeof(int32_t) * (size_t)(nnz_halo + 1)));
+  DevBuf recv_guard;
+  recv_guard.p = recv_cols;
+  int H = 0;
+  if (nnz_halo > 0) {
+    t = tmp_bytes;
+    cub::DeviceSelect::If(b_tmp.p, t, A->cols, b_rem.as<int>(), d_num, nz, IsRemote{lo, hi}, s);
+    size_t t2 = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, t2, b_rem.as<int>(), b_rem_sorted.as<int>(), nnz_halo, 0, 32, s);
+    DevBuf b_tmp2;
+    CGB_TRY(dev_alloc(b_tmp2, t2));
+    cub::DeviceRadixSort::SortKeys(b_tmp2.p, t2, b_rem.as<int>(), b_rem_sorted.as<int>(), nnz_halo, 0, 32, s);
+    size_t t3 = 0;
+    cub::DeviceSelect::Unique(nullptr, t3, b_rem_sorted.as<int>(), recv_cols, d_num, nnz_halo, s);
+    DevBuf b_tmp3;
+    CGB_TRY(dev_alloc(b_tmp3, t3));
+    cub::DeviceSelect::Unique(b_tmp3.p, t3, b_rem_sorted.as<int>(), recv_cols, d_num, nnz_halo, s);
+    CGB_TRY(read_int(ctx, d_num, &H));
+  }
+  d->H = H;
+
+  // fill both parts
+  int32_t *cols_loc = nullptr, *cols_halo = nullptr;
+  double *vals_loc = nullptr, *vals_halo = nullptr;
+  CGB_CUDA(cudaMalloc(&cols_loc, sizeof(int32_t) * (size_t)nnz_loc + 64));
+  CGB_CUDA(cudaMalloc(&vals_loc, sizeof(double) * (size_t)nnz_loc + 64));
+  CGB_CUDA(cudaMalloc(&cols_halo, sizeof(int32_t) * (size_t)nnz_halo + 64));
+  CGB_CUDA(cudaMalloc(&vals_halo, sizeof(double) * (size_t)nnz_halo + 64));
+  CGB_CUDA(cudaMalloc(&d->halo_rows, sizeof(int32_t) * (size_t)(nh + 1)));
+  if (n > 0) {
+    split_fill_kernel<<<gb, tb, 0, s>>>(n, A->rowptr, A->cols, A->vals, lo, hi, rowptr_loc, cols_loc, vals_loc, cnt_rem,
+                                        slot, rowptr_halo, cols_halo, vals_halo, d->halo_rows, recv_cols, H);
+    CGB_CUDA(cudaGetLastError());
+  }
+  CGB_TRY(cgb_csr_from_device(ctx, n, nnz_loc, vals_loc, cols_loc, rowptr_loc, 1, &d->Aloc));
+  CGB_TRY(cgb_csr_from_device(ctx, nh, nnz_halo, vals_halo, cols_halo, rowptr_halo, 1, &d->Ahalo));
+  d->Ahalo->n_cols = H;
+
+  // who sends what: receive counts per owner, all-gathered into a matrix
+  std::vector<int32_t> h_recv;
+  CGB_TRY(d2h_vec(ctx, h_recv, recv_cols, (size_t)H));
+  const int P = d->nranks;
+  d->rcount.assign(P, 0);
+  for (int32_t c : h_recv) {
+    const int q = owner_of(d->row_starts, c);
+    if (q < 0 || q >= P || q == d->rank) return fail(CGB_ERR_INVALID, "cgb_dist_create: column %d has no remote owner", c);
+    d->rcount[q]++;
+  }
+  d->roff.assign(P + 1, 0);
+  for (int q = 0; q < P; q++) d->roff[q + 1] = d->roff[q] + d->rcount[q];
+  DevBuf b_counts, b_matrix;
+  CGB_TRY(dev_alloc(b_counts, sizeof(int64_t) * (size_t)P));
+  CGB_TRY(dev_alloc(b_matrix, sizeof(int64_t) * (size_t)P * P));
+  CGB_CUDA(cudaMemcpyAsync(b_counts.p, d->rcount.data(), sizeof(int64_t) * (size_t)P, cudaMemcpyHostToDevice, s));
+  CGB_NCCL(g_nccl.AllGather(b_counts.p, b_matrix.p, (size_t)P, ncclInt64, d->comm, s));
+  std::vector<int64_t> M;
+  CGB_TRY(d2h_vec(ctx, M, b_matrix.as<int64_t>(), (size_t)P * P));
+  d->scount.assign(P, 0);
+  for (int q = 0; q < P; q++) d->scount[q] = M[(size_t)q * P + d->rank];
+  d->soff.assign(P + 1, 0);
+  for (int q = 0; q < P; q++) d->soff[q + 1] = d->soff[q] + d->scount[q];
+  d->S = d->soff[P];
+  CGB_CUDA(cudaMalloc(&d->send_idx, sizeof(int32_t) * (size_t)(d->S + 1)));
+  CGB_CUDA(cudaMalloc(&d->send_buf, sizeof(double) * (size_t)(d->S + 1)));
+  CGB_CUDA(cudaMalloc(&d->halo, sizeof(double) * (size_t)(H + 1)));
+  CGB_CUDA(cudaMemsetAsync(d->halo, 0, sizeof(double) * (size_t)(H + 1), s));
+  CGB_NCCL(g_nccl.GroupStart());
+  for (int q = 0; q < P; q++) {
+    if (d->rcount[q] > 0) CGB_NCCL(g_nccl.Send(recv_cols + d->roff[q], (size_t)d->rcount[q], ncclInt32, q, d->comm, s));
+    if (d->scount[q] > 0) CGB_NCCL(g_nccl.Recv(d->send_idx + d->soff[q], (size_t)d->scount[q], ncclInt32, q, d->comm, s));
+  }
+  CGB_NCCL(g_nccl.GroupEnd());
+  if (d->S > 0) {
+    rebase_kernel<<<(unsigned)((d->S + tb - 1) / tb), tb, 0, s>>>(d->send_idx, d->S, lo);
+    CGB_CUDA(cudaGetLastError());
+  }
+  CGB_CUDA(cudaStreamSynchronize(s));
+  return CGB_OK;
+}
+
+struct DistLoop {
+  cudaGraphExec_t graph = nullptr;
+};
+
+int dist_enqueue_iteration(cgb_dist *d, double *x) {
+  cgb_csr *A = d->Aloc;
+  Workspace &w = A->ws;
+  cudaStream_t s = d->ctx->stream;
+  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  cg_pupdate_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
+  CGB_TRY(halo_exchange(d, w.p0, 1));
+  CGB_LAUNCH_LB(A->lanes, false, cg_spmv_kernel, A->grid_spmv, s, V, w.r, w.p0, w.p1, w.Ap, w.st, w.partials, d->scal + 0);
+  CGB_TRY(halo_apply(d, w.Ap, w.p0, d->scal + 0, d->scal + 0, 1));
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 0, d->scal + 1, 1, ncclDouble, ncclSum, d->comm, s));
+  cg_update_kernel<false><<<A->grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
+                                                         d->scal + 1, d->scal + 2);
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 2, d->scal + 3, 1, ncclDouble, ncclSum, d->comm, s));
+  cg_advance_kernel<<<1, 32, 0, s>>>(w.st, d->scal + 3, w.hist);
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int cgb_dist_create(cgb_ctx *ctx, int rank, int nranks, const void *h_id128, const int64_t *row_starts,
+                    cgb_csr *A, cgb_dist **out) {
+  CGB_REQUIRE(ctx && h_id128 && row_starts && A && out, "cgb_dist_create: NULL argument");
+  CGB_REQUIRE(nranks >= 1 && rank >= 0 && rank < nranks, "cgb_dist_create: bad rank");
+  CGB_REQUIRE(row_starts[rank + 1] - row_starts[rank] == A->n, "cgb_dist_create: row block size mismatch");
+  CGB_REQUIRE(row_starts[nranks] < ((int64_t)1 << 31), "cgb_dist_create: global size must fit 32-bit columns");
+  *out = nullptr;
+  CGB_TRY(nccl_load());
+  ScopedDevice sd(ctx->device);
+  cgb_dist *d = new cgb_dist();
+  d->ctx = ctx;
+  d->rank = rank;
+  d->nranks = nranks;
+  d->n = A->n;
+  d->row_starts.assign(row_starts, row_starts + nranks + 1);
+  int rc = CGB_OK;
+  do {
+    ncclUniqueId id;
+    memcpy(&id, h_id128, sizeof(id));
+    ncclResult_t r = g_nccl.CommInitRank(&d->comm, nranks, id, rank);
+    if (r != ncclSuccess) {
+      rc = fail(CGB_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+      d->comm = nullptr;
+      break;
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&d->comm_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_pack, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMalloc(&d->scal, sizeof(double) * 8);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->scal, 0, sizeof(double) * 8, ctx->stream);
+    if (e != cudaSuccess) {
+      rc = fail(CGB_ERR_CUDA, "cgb_dist_create: %s", cudaGetErrorString(e));
+      break;
+    }
+    rc = dist_setup(d, A);
+  } while (0);
+  if (rc != CGB_OK) {
+    std::string keep = cgb_last_error();
+    cgb_dist_destroy(d);
+    set_error("%s", keep.c_str());
+    return rc;
+  }
+  *out = d;
+  return CGB_OK;
+}
+
+int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,
+                      const cgb_cg_opts *opts_in, cgb_cg_stats *stats) {
+  CGB_REQUIRE(d, "cgb_dist_cg_solve: handle is NULL");
+  if (!d_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");
+  CGB_REQUIRE(d_x, "cgb_dist_cg_solve: x is NULL");
+  cgb_cg_opts o;
+  if (opts_in) o = *opts_in; else cgb_cg_default_opts(&o);
+  if (stats) memset(stats, 0, sizeof(*stats));
+  cgb_ctx *ctx = d->ctx;
+  cgb_csr *A = d->Aloc;
+  const int64_t n = A->n, n_global = d->row_starts[d->nranks];
+  if (max_iter < 0) max_iter = n_global + 1;
+  ScopedDevice sd(ctx->device);
+  cudaStream_t s = ctx->stream;
+  int batch = o.check_every > 0 ? o.check_every : 32;
+  if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
+  const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
+  CGB_TRY(workspace_ensure(A, n, false, hist_cap));
+  Workspace &w = A->ws;
+  const bool use_graph = o.loop_mode != CGB_LOOP_STEPWISE;
+
+  cudaEvent_t t0, t1;
+  CGB_CUDA(cudaEventCreate(&t0));
+  CGB_CUDA(cudaEventCreate(&t1));
+  struct G {
+    cudaEvent_t a, b;
+    ~G() { cudaEventDestroy(a); cudaEventDestroy(b); }
+  } guard{t0, t1};
+  CGB_CUDA(cudaEventRecord(t0, s));
+  CgState init;
+  memset(&init, 0, sizeof(init));
+  init.tol = abs_tol;
+  init.max_iter = max_iter;
+  init.record_history = o.record_history ? 1 : 0;
+  init.hist_cap = w.hist_cap;
+  init.done = 1;
+  w.h_st[0] = init;
+  CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
+  CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)std::max<int64_t>(n, 1), s));
+  // K0: r = b - A x0 (halo of x0 first), rr = allreduce(r.r)
+  CGB_TRY(halo_exchange(d, d_x, 0));
+  if (n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
+  CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
+  dist_init_kernel<<<A->grid_vec, kBlock, 0, s>>>(n, d_b, w.Ap, w.r, w.st, w.partials, d->scal + 2);
+  CGB_CUDA(cudaGetLastError());
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 2, d->scal + 3, 1, ncclDouble, ncclSum, d->comm, s));
+  dist_arm_kernel<<<1, 32, 0, s>>>(w.st, d->scal + 3, w.hist);
+  CGB_CUDA(cudaGetLastError());
+
+  int64_t launches = 6;
+  if (use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != (uint64_t)batch)) {
+    if (w.graph) {
+      cudaGraphExecDestroy(w.graph);
+      w.graph = nullptr;
+    }
+    cudaGraph_t g = nullptr;
+    CGB_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int rc = CGB_OK;
+    for (int i = 0; i < batch && rc == CGB_OK; i++) rc = dist_enqueue_iteration(d, d_x);
+    cudaError_t e = cudaStreamEndCapture(s, &g);
+    if (rc != CGB_OK) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "cudaStreamEndCapture (dist): %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&w.graph, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+      w.graph = nullptr;
+      return fail(CGB_ERR_CUDA, "cudaGraphInstantiate (dist): %s", cudaGetErrorString(e));
+    }
+    w.graph_key = (uint64_t)batch;
+    w.graph_x = d_x;
+  }
+  // every rank takes the same decisions: the polled state is built from all-reduced scalars only
+  while (true) {
+    if (use_graph) {
+      CGB_CUDA(cudaGraphLaunch(w.graph, s));
+    } else {
+      for (int i = 0; i < batch; i++) CGB_TRY(dist_enqueue_iteration(d, d_x));
+    }
+    launches += (int64_t)batch * 6;
+    CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+    CGB_CUDA(cudaStreamSynchronize(s));
+    if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter) break;
+  }
+  CGB_CUDA(cudaEventRecord(t1, s));
+  CGB_CUDA(cudaEventSynchronize(t1));
+  const CgState &f = w.h_st[0];
+  w.hist_count = o.record_history ? std::min<int64_t>(f.iter + 1, w.hist_cap) : 0;
+  if (stats) {
+    float ms = 0.f;
+    CGB_CUDA(cudaEventElapsedTime(&ms, t0, t1));
+    stats->iterations = f.iter;
+    stats->rr = f.rr;
+    stats->rr0 = f.rr0;
+    stats->converged = f.done;
+    stats->nan_stop = f.nan_stop;
+    stats->solve_ms = ms;
+    stats->kernel_launches = launches;
+    stats->loop_mode = use_graph ? CGB_LOOP_GRAPH : CGB_LOOP_STEPWISE;
+    stats->format = CGB_FMT_CSR;
+  }
+  return CGB_OK;
+}
+
+int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double *rr, double *xx) {
+  CGB_REQUIRE(d && d_x && d_b && rr && xx, "cgb_dist_residual: NULL argument");
+  cgb_ctx *ctx = d->ctx;
+  cgb_csr *A = d->Aloc;
+  ScopedDevice sd(ctx->device);
+  cudaStream_t s = ctx->stream;
+  CGB_TRY(workspace_ensure(A, A->n, false, 0));
+  Workspace &w = A->ws;
+  CGB_TRY(halo_exchange(d, d_x, 0));
+  if (A->n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
+  CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
+  dist_resid_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, d_b, w.Ap, d_x, w.st, w.partials, d->scal + 4);
+  CGB_CUDA(cudaGetLastError());
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 4, d->scal + 4, 2, ncclDouble, ncclSum, d->comm, s));
+  CGB_CUDA(cudaMemcpyAsync(ctx->pinned, d->scal + 4, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CGB_CUDA(cudaStreamSynchronize(s));
+  *rr = ctx->pinned[0];
+  *xx = ctx->pinned[1];
+  return CGB_OK;
+}
+
+} // extern "C"

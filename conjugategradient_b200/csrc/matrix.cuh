@@ -1,0 +1,62 @@
+// matrix.cuh — the device CSR handle (replaces CGSolver::Matrix, reference
+// src/LinearAlgebraTypes.hpp:57-132) plus the launch plan and the cached CG workspace.
+#pragma once
+#include "common.cuh"
+
+namespace cgb {
+
+// Work vectors and scalars of CG::solve (reference allocates them per solve, twice:
+// src/CG.hpp:276-301); here they live with the matrix and are reused across solves.
+struct Workspace {
+  int64_t n = 0;       // rows
+  int64_t n_ext = 0;   // rows + halo slots (multi-GPU), == n on one GPU
+  double *r = nullptr;
+  double *p0 = nullptr; // p (unfused) / ping
+  double *p1 = nullptr; // pong (fused p-update only, lazily allocated)
+  double *Ap = nullptr;
+  CgState *st = nullptr;
+  double *partials = nullptr; // kMaxPartials * 2
+  double *hist = nullptr;
+  int64_t hist_cap = 0;
+  int64_t hist_count = 0;
+  CgState *h_st = nullptr; // pinned mirror for polling
+  // cached CUDA graphs of one batch of iterations, keyed by the launch configuration
+  cudaGraphExec_t graph = nullptr;
+  uint64_t graph_key = 0;
+  const double *graph_x = nullptr; // the x pointer baked into the graph
+  // kernel timing events (time_kernels)
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+} // namespace cgb
+
+struct cgb_csr {
+  cgb_ctx *ctx = nullptr;
+  int64_t n = 0;
+  int64_t nnz = 0;
+  int64_t n_cols = 0; // length the gathered vector must have (n, or n + halo for a local block)
+  double *vals = nullptr;
+  int32_t *cols = nullptr;
+  int32_t *rowptr = nullptr;
+  bool owns = false;
+  int format = CGB_FMT_AUTO;
+  // plan
+  int lanes = 8;       // lanes per row of the CSR kernel
+  int grid_spmv = 0;   // CTAs for SpMV-shaped kernels
+  int grid_vec = 0;    // CTAs for streaming vector kernels
+  // SELL-C-sigma shadow copy
+  int sell_sigma = 0;
+  int64_t sell_slices = 0;
+  int64_t sell_padded = 0;
+  double *sell_vals = nullptr;
+  int32_t *sell_cols = nullptr;
+  int64_t *sell_off = nullptr;  // slice offsets (in entries), sell_slices + 1
+  int32_t *sell_perm = nullptr; // slot -> row (NULL when sigma == 1)
+  cgb::Workspace ws;
+};
+
+namespace cgb {
+int csr_plan(cgb_csr *A);
+int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap);
+void workspace_release(cgb_csr *A);
+} // namespace cgb

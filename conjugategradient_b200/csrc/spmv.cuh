@@ -1,0 +1,143 @@
+// spmv.cuh — CSR SpMV device code with pluggable gather and per-row epilogue.
+//
+// One body serves every SpMV-shaped pass of the path:
+//   y = A x                         VectorOperations::spmv        (reference src/VectorOperations.hpp:455-462)
+//   Ap = A p, partial p.Ap          CG loop steps 3+4             (src/CG.hpp:374-379)
+//   r = b - A x0, partial r.r       CG set-up                     (src/CG.hpp:324-341)
+//   sum (b - A x)^2, sum x^2        CG::accuracy                  (src/CG.hpp:477-499)
+// Row sums use L lanes per row (L = 1 .. 32, chosen from the mean row length), values and column
+// indices are streamed with L1::no_allocate loads, the gathered vector goes through L1/L2.
+#pragma once
+#include "common.cuh"
+
+namespace cgb {
+
+// ---- gathers --------------------------------------------------------------------------------
+struct GatherPlain {
+  const double *x;
+  __device__ __forceinline__ double operator()(int c) const { return __ldg(x + c); }
+};
+// p = r + beta * p_old formed on the fly (fused p-update); same rounding as the epilogue's p_new.
+struct GatherFusedP {
+  const double *r;
+  const double *p_old;
+  double beta;
+  __device__ __forceinline__ double operator()(int c) const { return fma(beta, __ldg(p_old + c), __ldg(r + c)); }
+};
+
+// ---- per-row epilogues: row(i, sum) consumes the finished row sum; acc0/acc1 are the thread's
+// contributions to up to two fused reductions ----------------------------------------------------
+struct EpiStore {
+  static constexpr int NRED = 0;
+  double *y;
+  __device__ __forceinline__ void row(int64_t i, double s, double &, double &) const { y[i] = s; }
+};
+struct EpiDotP { // Ap[i] = s ; acc0 += p[i] * s
+  static constexpr int NRED = 1;
+  double *y;
+  const double *p;
+  __device__ __forceinline__ void row(int64_t i, double s, double &a0, double &) const {
+    y[i] = s;
+    a0 += p[i] * s;
+  }
+};
+struct EpiDotFusedP { // p_new[i] = r[i] + beta p_old[i] ; Ap[i] = s ; acc0 += p_new[i] * s
+  static constexpr int NRED = 1;
+  double *y;
+  const double *r;
+  const double *p_old;
+  double *p_new;
+  double beta;
+  __device__ __forceinline__ void row(int64_t i, double s, double &a0, double &) const {
+    const double pn = fma(beta, p_old[i], r[i]);
+    p_new[i] = pn;
+    y[i] = s;
+    a0 += pn * s;
+  }
+};
+struct EpiInitResidual { // r[i] = b[i] - s ; acc0 += r[i]^2      (src/CG.hpp:324-332, :341)
+  static constexpr int NRED = 1;
+  const double *b;
+  double *r;
+  __device__ __forceinline__ void row(int64_t i, double s, double &a0, double &) const {
+    const double ri = b[i] - s;
+    r[i] = ri;
+    a0 += ri * ri;
+  }
+};
+struct EpiAccuracy { // acc0 += (b[i]-s)^2 ; acc1 += x[i]^2        (src/CG.hpp:487-498)
+  static constexpr int NRED = 2;
+  const double *b;
+  const double *x;
+  __device__ __forceinline__ void row(int64_t i, double s, double &a0, double &a1) const {
+    const double a = b[i] - s;
+    a0 += a * a;
+    a1 += x[i] * x[i];
+  }
+};
+
+// ---- L lanes per row, direct loads ------------------------------------------------------------
+// Rows [row_lo, row_hi) are dealt to lane groups round-robin over (bid, nb) CTAs; two rows per
+// group are in flight at a time.  All 32 lanes of a warp take every shuffle.
+template <int L, class G, class E>
+__device__ __forceinline__ void spmv_rows_vec(int64_t row_lo, int64_t row_hi, const int *__restrict__ rowptr,
+                                              const int *__restrict__ cols, const double *__restrict__ vals,
+                                              const G &g, const E &e, int bid, int nb, double &a0, double &a1) {
+  constexpr int GPW = 32 / L; // groups per warp
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % L;
+  const int grp = lane / L;
+  const int64_t warp_id = (int64_t)bid * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)nb * (blockDim.x >> 5);
+  const int64_t stride = nwarps * GPW;
+  for (int64_t base = row_lo + warp_id * GPW; base < row_hi; base += 2 * stride) {
+    const int64_t r0 = base + grp, r1 = base + stride + grp;
+    int s0 = 0, e0 = 0, s1 = 0, e1 = 0;
+    if (r0 < row_hi) {
+      s0 = __ldg(rowptr + r0);
+      e0 = __ldg(rowptr + r0 + 1);
+    }
+    if (r1 < row_hi) {
+      s1 = __ldg(rowptr + r1);
+      e1 = __ldg(rowptr + r1 + 1);
+    }
+    double sum0 = 0.0, sum1 = 0.0;
+    int j0 = s0 + sub, j1 = s1 + sub;
+    // both rows advance together while both have entries, so their loads overlap
+    while (j0 < e0 && j1 < e1) {
+      const int c0 = ld_stream_s32(cols + j0), c1 = ld_stream_s32(cols + j1);
+      const double v0 = ld_stream_f64(vals + j0), v1 = ld_stream_f64(vals + j1);
+      sum0 = fma(v0, g(c0), sum0);
+      sum1 = fma(v1, g(c1), sum1);
+      j0 += L;
+      j1 += L;
+    }
+    for (; j0 < e0; j0 += L) sum0 = fma(ld_stream_f64(vals + j0), g(ld_stream_s32(cols + j0)), sum0);
+    for (; j1 < e1; j1 += L) sum1 = fma(ld_stream_f64(vals + j1), g(ld_stream_s32(cols + j1)), sum1);
+#pragma unroll
+    for (int o = L >> 1; o > 0; o >>= 1) {
+      sum0 += __shfl_down_sync(0xffffffffu, sum0, o, L);
+      sum1 += __shfl_down_sync(0xffffffffu, sum1, o, L);
+    }
+    if (sub == 0) {
+      if (r0 < row_hi) e.row(r0, sum0, a0, a1);
+      if (r1 < row_hi) e.row(r1, sum1, a0, a1);
+    }
+  }
+}
+
+template <class G, class E>
+__device__ __forceinline__ void spmv_rows_dispatch(int lanes, int64_t row_lo, int64_t row_hi, const int *rowptr,
+                                                   const int *cols, const double *vals, const G &g, const E &e,
+                                                   int bid, int nb, double &a0, double &a1) {
+  switch (lanes) {
+  case 1: spmv_rows_vec<1>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  case 2: spmv_rows_vec<2>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  case 4: spmv_rows_vec<4>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  case 8: spmv_rows_vec<8>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  case 16: spmv_rows_vec<16>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  default: spmv_rows_vec<32>(row_lo, row_hi, rowptr, cols, vals, g, e, bid, nb, a0, a1); break;
+  }
+}
+
+} // namespace cgb

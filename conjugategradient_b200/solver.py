@@ -1,0 +1,325 @@
+"""Python harness over the C-ABI, mirroring the reference's C++ API names so tests read like the
+reference's driver (reference test/Tester.cpp:36-53, src/CG.hpp:53-601, src/VectorOperations.hpp).
+
+Nothing here computes: every method forwards to libcgb200.so (CUDA, sm_100a).  NumPy arrays are
+host buffers only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """Device + stream (reference: acpp::sycl::queue, src/CG.hpp:61,70-77)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = L.load()
+        h = C.c_void_p()
+        L.check(self.lib.cgb_ctx_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.lib.cgb_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        L.check(self.lib.cgb_ctx_sync(self.h))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.cgb_ctx_stream(self.h) or 0)
+
+    @property
+    def sm_count(self) -> int:
+        return self.lib.cgb_ctx_sm_count(self.h)
+
+    # -- raw buffers -------------------------------------------------------------------------
+    def malloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        L.check(self.lib.cgb_malloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def free(self, ptr):
+        if ptr:
+            L.check(self.lib.cgb_free(self.h, ptr))
+
+
+class Vector:
+    """Device vector of doubles (reference: CGSolver::Vector, src/LinearAlgebraTypes.hpp:143-203)."""
+
+    def __init__(self, ctx: Context, data=None, n: int | None = None):
+        self.ctx = ctx
+        if data is not None:
+            data = _f64(data)
+            n = data.size
+        self.n = int(n)
+        self.ptr = ctx.malloc(8 * max(self.n, 1))
+        if data is not None:
+            self.upload(data)
+        else:
+            L.check(ctx.lib.cgb_memset(ctx.h, self.ptr, 0, 8 * self.n))
+
+    def upload(self, data):
+        data = _f64(data)
+        assert data.size == self.n
+        L.check(self.ctx.lib.cgb_memcpy_h2d(self.ctx.h, self.ptr, _p(data), 8 * self.n, 1))
+
+    def download(self) -> np.ndarray:
+        out = np.empty(self.n)
+        L.check(self.ctx.lib.cgb_memcpy_d2h(self.ctx.h, _p(out), self.ptr, 8 * self.n, 1))
+        return out
+
+    def free(self):
+        if self.ptr:
+            self.ctx.free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Scalar(Vector):
+    """One device scalar (reference: CGSolver::Scalar, src/LinearAlgebraTypes.hpp:210-250)."""
+
+    def __init__(self, ctx: Context, value: float = 0.0):
+        super().__init__(ctx, data=np.array([value]))
+
+    @property
+    def value(self) -> float:
+        v = C.c_double()
+        L.check(self.ctx.lib.cgb_scalar_get(self.ctx.h, self.ptr, C.byref(v)))
+        return v.value
+
+    def set(self, value: float):
+        L.check(self.ctx.lib.cgb_scalar_set(self.ctx.h, self.ptr, float(value)))
+
+
+class Matrix:
+    """Device CSR matrix (reference: CGSolver::Matrix, src/LinearAlgebraTypes.hpp:57-132)."""
+
+    def __init__(self, ctx: Context, data=None, cols=None, rows=None, handle=None):
+        self.ctx = ctx
+        if handle is None:
+            data, cols, rows = _f64(data), _i32(cols), _i32(rows)
+            h = C.c_void_p()
+            L.check(ctx.lib.cgb_csr_create(ctx.h, rows.size - 1, data.size, _p(data), _p(cols), _p(rows), C.byref(h)))
+            handle = h
+        self.h = handle
+
+    @classmethod
+    def stencil(cls, ctx: Context, kind: str, m: int, mz: int = 0, row_begin: int = 0, row_end: int = -1):
+        k = {"2d5": 0, "3d7": 1, "3d27": 2}[kind]
+        h = C.c_void_p()
+        L.check(ctx.lib.cgb_gen_stencil(ctx.h, k, m, mz, row_begin, row_end, C.byref(h)))
+        return cls(ctx, handle=h)
+
+    def N(self) -> int:
+        return int(self.ctx.lib.cgb_csr_n(self.h))
+
+    def NNZ(self) -> int:
+        return int(self.ctx.lib.cgb_csr_nnz(self.h))
+
+    def to_host(self):
+        n, nnz = self.N(), self.NNZ()
+        vals, cols, rows = np.empty(nnz), np.empty(nnz, np.int32), np.empty(n + 1, np.int32)
+        lib, c = self.ctx.lib, self.ctx.h
+        L.check(lib.cgb_memcpy_d2h(c, _p(vals), lib.cgb_csr_vals(self.h), 8 * nnz, 1))
+        L.check(lib.cgb_memcpy_d2h(c, _p(cols), lib.cgb_csr_cols(self.h), 4 * nnz, 1))
+        L.check(lib.cgb_memcpy_d2h(c, _p(rows), lib.cgb_csr_rowptr(self.h), 4 * (n + 1), 1))
+        return vals, cols, rows
+
+    def set_format(self, fmt: int, sigma: int = 1):
+        if fmt == L.FMT_SELL:
+            L.check(self.ctx.lib.cgb_csr_build_sell(self.h, sigma))
+        L.check(self.ctx.lib.cgb_csr_set_format(self.h, fmt))
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.cgb_csr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class VectorOperations:
+    """Per-op kernels (reference: CGSolver::VectorOperations, src/VectorOperations.hpp:39-488)."""
+
+    def __init__(self, ctx: Context):
+        self.ctx = ctx
+        self.vector_size = 0
+
+    def setVectorSize(self, n: int):
+        self.vector_size = int(n)
+
+    def spmv(self, A: Matrix, vec: Vector, result: Vector):
+        assert self.vector_size != 0 and A.N() == self.vector_size  # reference :444
+        L.check(self.ctx.lib.cgb_spmv(self.ctx.h, A.h, vec.ptr, result.ptr))
+
+    def dot_product_trivial(self, left: Vector, right: Vector, result: Scalar):
+        L.check(self.ctx.lib.cgb_dot_acc(self.ctx.h, self.vector_size, left.ptr, right.ptr, result.ptr))
+
+    dot_product_optimised = dot_product_trivial
+    dot_product = dot_product_trivial
+
+    def norm(self, vec: Vector, result: Scalar):
+        L.check(self.ctx.lib.cgb_norm2_acc(self.ctx.h, self.vector_size, vec.ptr, result.ptr))
+
+    def saxpby(self, X: Vector, Y: Vector, a: Scalar, b: Scalar, result: Vector):
+        L.check(self.ctx.lib.cgb_axpby(self.ctx.h, self.vector_size, X.ptr, Y.ptr, a.ptr, b.ptr, result.ptr))
+
+    def sapbx(self, X: Vector, Y: Vector, b: Scalar, result: Vector):
+        L.check(self.ctx.lib.cgb_xpby(self.ctx.h, self.vector_size, X.ptr, Y.ptr, b.ptr, 1, result.ptr))
+
+    def sambx(self, X: Vector, Y: Vector, b: Scalar, result: Vector):
+        L.check(self.ctx.lib.cgb_xpby(self.ctx.h, self.vector_size, X.ptr, Y.ptr, b.ptr, -1, result.ptr))
+
+
+def make_opts(**kw) -> L.CgOpts:
+    o = L.CgOpts()
+    L.load().cgb_cg_default_opts(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise TypeError(f"unknown CG option {k}")
+        setattr(o, k, int(v))
+    return o
+
+
+class CG:
+    """Reference-shaped solver object (reference: CGSolver::CG, src/CG.hpp:53-601)."""
+
+    def __init__(self, ctx: Context | None = None, **opts):
+        self.ctx = ctx or Context(0)
+        self.A: Matrix | None = None
+        self.b: Vector | None = None
+        self.x: Vector | None = None
+        self.opts = opts
+        self.stats: dict | None = None
+
+    @classmethod
+    def createCG(cls, **opts):
+        return cls(Context(0), **opts)
+
+    def setMatrix(self, data, columns=None, rows=None):
+        self.A = data if isinstance(data, Matrix) else Matrix(self.ctx, data, columns, rows)
+
+    def getDimension(self) -> int:
+        return self.A.N() if self.A is not None else 0
+
+    def setTarget(self, data):
+        self.b = data if isinstance(data, Vector) else Vector(self.ctx, data)
+
+    def setInital(self, data):  # sic — the reference spells it this way (src/CG.hpp:215)
+        self.x = data if isinstance(data, Vector) else Vector(self.ctx, data)
+
+    setInitial = setInital
+
+    def calculateExpectedStepCount(self, accuracy):  # no-op in the reference too (src/CG.hpp:235)
+        return None
+
+    def solve(self, improvement: float = 0.0, max_iter: int = -1):
+        if self.b is None:
+            raise RuntimeError("No right hand side to solve for")  # src/CG.hpp:266-268
+        if self.A is None:
+            raise RuntimeError("No Matrix given")  # src/CG.hpp:270-272
+        if self.x is None:
+            self.x = Vector(self.ctx, n=self.A.N())  # zeros (src/CG.hpp:291-297)
+        o = make_opts(**self.opts)
+        st = L.CgStats()
+        L.check(self.ctx.lib.cgb_cg_solve(self.ctx.h, self.A.h, self.b.ptr, self.x.ptr, float(improvement),
+                                          int(max_iter), C.byref(o), C.byref(st)))
+        self.stats = st.as_dict()
+        return self.stats
+
+    def history(self) -> np.ndarray:
+        cnt = C.c_int64()
+        L.check(self.ctx.lib.cgb_cg_history(self.ctx.h, self.A.h, None, 0, C.byref(cnt)))
+        out = np.empty(cnt.value)
+        if cnt.value:
+            L.check(self.ctx.lib.cgb_cg_history(self.ctx.h, self.A.h, _p(out), cnt.value, C.byref(cnt)))
+        return out
+
+    def accuracy(self) -> float:
+        rr, xx = self.residual()
+        return abs(rr / xx) if xx != 0 else abs(np.float64(rr) / np.float64(xx))
+
+    def residual(self):
+        rr, xx = C.c_double(), C.c_double()
+        L.check(self.ctx.lib.cgb_residual(self.ctx.h, self.A.h, self.x.ptr, self.b.ptr, C.byref(rr), C.byref(xx)))
+        return rr.value, xx.value
+
+    def extract(self) -> np.ndarray:
+        return self.x.download()
+
+    def extractTo(self, out: np.ndarray):
+        out[...] = self.x.download()
+
+    def memoryFootprint(self) -> int:
+        return int(self.ctx.lib.cgb_memory_footprint(self.A.N(), self.A.NNZ()))
+
+    # additive accessors (the reference returns none of these)
+    def iterations(self) -> int:
+        return int(self.stats["iterations"]) if self.stats else 0
+
+    def residualNorm(self) -> float:
+        return float(np.sqrt(self.stats["rr"])) if self.stats else float("nan")
+
+
+def solve_host(ctx: Context, vals, cols, rows, b, tol, x0=None, max_iter=-1, **opts):
+    """Host-buffer solve through cgb_cg_solve_host (the end-to-end path)."""
+    vals, cols, rows, b = _f64(vals), _i32(cols), _i32(rows), _f64(b)
+    n = rows.size - 1
+    x = np.empty(n)
+    x0a = None if x0 is None else _f64(x0)
+    o = make_opts(**opts)
+    st = L.CgStats()
+    L.check(ctx.lib.cgb_cg_solve_host(ctx.h, n, vals.size, _p(vals), _p(cols), _p(rows), _p(b),
+                                      None if x0a is None else _p(x0a), _p(x), float(tol), int(max_iter),
+                                      C.byref(o), C.byref(st)))
+    return x, st.as_dict()
+
+
+def mm_read(path: str):
+    """Matrix Market -> CSR through the library's dialect-compatible reader (test/mm_reader.cpp:154)."""
+    import os
+    lib = L.load()
+    h = C.c_void_p()
+    L.check(lib.cgb_mm_read(os.fsencode(path), C.byref(h)))
+    try:
+        n, nnz = lib.cgb_mm_n(h), lib.cgb_mm_nnz(h)
+        vals = np.ctypeslib.as_array(C.cast(lib.cgb_mm_vals(h), L.c_dp), shape=(nnz,)).copy()
+        cols = np.ctypeslib.as_array(C.cast(lib.cgb_mm_cols(h), L.c_ip), shape=(nnz,)).copy()
+        rows = np.ctypeslib.as_array(C.cast(lib.cgb_mm_rowptr(h), L.c_ip), shape=(n + 1,)).copy()
+    finally:
+        lib.cgb_mm_free(h)
+    return vals, cols, rows

@@ -14,8 +14,7 @@ namespace cgb {
 struct LoopCfg {
   bool fused;
   bool time_kernels;
-  int lanes;
-  int grid_spmv;
+  SpmvLaunch sl;
   int grid_vec;
 };
 
@@ -23,15 +22,23 @@ struct LoopCfg {
 // (legal inside stream capture; they become event-record nodes of the graph).
 static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream_t s, bool timed) {
   Workspace &w = A->ws;
-  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  const CsrView V = csr_view(A);
   auto mark = [&](int i) -> cudaError_t {
     return timed ? cudaEventRecordWithFlags(w.ev[i], s, cudaEventRecordExternal) : cudaSuccess;
   };
   CGB_CUDA(mark(0));
   if (!c.fused) cg_pupdate_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
   CGB_CUDA(mark(1));
-  CGB_LAUNCH_LB(c.lanes, c.fused, cg_spmv_kernel, c.grid_spmv, s, V, w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
-                (double *)nullptr);
+  dispatch_lanes(c.sl.lanes, c.sl.tma, [&](auto Lc, auto Tc) {
+    constexpr int L = decltype(Lc)::value;
+    constexpr bool T = decltype(Tc)::value;
+    if (c.fused)
+      launch_kernel(cg_spmv_kernel<L, T, true>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
+                    (double *)nullptr);
+    else
+      launch_kernel(cg_spmv_kernel<L, T, false>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
+                    (double *)nullptr);
+  });
   CGB_CUDA(mark(2));
   if (c.fused)
     cg_update_kernel<true><<<c.grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
@@ -109,7 +116,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
-  LoopCfg cfg{fused, o.time_kernels != 0, A->lanes, A->grid_spmv, A->grid_vec};
+  LoopCfg cfg{fused, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec};
   if (cfg.time_kernels)
     for (auto &e : w.ev)
       if (!e) CGB_CUDA(cudaEventCreate(&e));
@@ -138,8 +145,10 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
   CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)n, s));
   if (fused) CGB_CUDA(cudaMemsetAsync(w.p1, 0, sizeof(double) * (size_t)n, s));
-  CsrView V{n, A->rowptr, A->cols, A->vals};
-  CGB_LAUNCH_L(A->lanes, cg_init_kernel, A->grid_spmv, s, V, (const double *)d_x, d_b, w.r, w.st, w.partials, w.hist);
+  dispatch_lanes(cfg.sl.lanes, cfg.sl.tma, [&](auto Lc, auto Tc) {
+    launch_kernel(cg_init_kernel<decltype(Lc)::value, decltype(Tc)::value>, cfg.sl, s, csr_view(A), (const double *)d_x,
+                  d_b, w.r, w.st, w.partials, w.hist);
+  });
   CGB_CUDA(cudaGetLastError());
   int64_t launches = 1;
 
@@ -147,8 +156,8 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   double t_p = 0, t_s = 0, t_u = 0;
   int64_t samples = 0;
   if (mode == CGB_LOOP_GRAPH) {
-    const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.lanes << 8) ^ ((uint64_t)fused << 1) ^
-                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.grid_spmv << 16);
+    const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
+                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.tma << 2);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an

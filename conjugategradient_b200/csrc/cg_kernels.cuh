@@ -12,16 +12,30 @@
 // stop test has fired or the trip cap is reached, later launches return immediately, so a CUDA
 // graph holding a batch of iterations can overshoot harmlessly.
 #pragma once
-#include "spmv.cuh"
+#include "spmv_tma.cuh"
 
 namespace cgb {
 
 struct CsrView {
   int64_t n;
+  int64_t nnz;
   const int *rowptr;
   const int *cols;
   const double *vals;
 };
+
+// One entry point for both row engines: TMA-staged tiles (288 threads, dynamic shared memory) or
+// direct loads with L lanes per row (256 threads).
+template <int L, bool TMA, class G, class E>
+__device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E &e, double &a0, double &a1) {
+  if constexpr (TMA) {
+    extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
+    spmv_rows_tma<L>(A.n, A.nnz, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
+  } else {
+    spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  }
+}
+#define CGB_BOUNDS(TMA) __launch_bounds__((TMA) ? kTmaThreads : kBlock)
 
 __device__ __forceinline__ bool cg_active(const CgState *st) {
   // reference: do { ... } while (counter++ < N && !*is_done)   (src/CG.hpp:436)
@@ -29,15 +43,15 @@ __device__ __forceinline__ bool cg_active(const CgState *st) {
 }
 
 // ---- K0 -------------------------------------------------------------------------------------
-template <int L>
-__global__ void __launch_bounds__(kBlock) cg_init_kernel(CsrView A, const double *__restrict__ x,
+template <int L, bool TMA>
+__global__ void CGB_BOUNDS(TMA) cg_init_kernel(CsrView A, const double *__restrict__ x,
                                                           const double *__restrict__ b, double *__restrict__ r,
                                                           CgState *st, double *partials, double *hist) {
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiInitResidual e{b, r};
-  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  spmv_rows<L, TMA>(A, g, e, a0, a1);
   a0 = block_sum(a0, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = a0;
   if (publish_and_elect(&st->ticket, gridDim.x)) {
@@ -77,8 +91,8 @@ static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, co
 
 // ---- K1 -------------------------------------------------------------------------------------
 // FUSED: p buffers ping-pong on the iteration parity; p_old = pbuf[iter & 1], p_new = pbuf[~iter & 1].
-template <int L, bool FUSED>
-__global__ void __launch_bounds__(kBlock) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
+template <int L, bool TMA, bool FUSED>
+__global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
                                                           double *pbuf1, double *__restrict__ Ap, CgState *st,
                                                           double *partials, double *local_out) {
   if (!cg_active(st)) return;
@@ -91,11 +105,11 @@ __global__ void __launch_bounds__(kBlock) cg_spmv_kernel(CsrView A, const double
     const double beta = st->beta;
     GatherFusedP g{r, p_old, beta};
     EpiDotFusedP e{Ap, r, p_old, p_new, beta};
-    spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+    spmv_rows<L, TMA>(A, g, e, a0, a1);
   } else {
     GatherPlain g{pbuf0};
     EpiDotP e{Ap, pbuf0};
-    spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+    spmv_rows<L, TMA>(A, g, e, a0, a1);
   }
   a0 = block_sum(a0, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = a0;
@@ -194,15 +208,15 @@ static __global__ void cg_advance_kernel(CgState *st, const double *rr_global, d
 }
 
 // ---- K4 -------------------------------------------------------------------------------------
-template <int L>
-__global__ void __launch_bounds__(kBlock) residual_kernel(CsrView A, const double *__restrict__ x,
+template <int L, bool TMA>
+__global__ void CGB_BOUNDS(TMA) residual_kernel(CsrView A, const double *__restrict__ x,
                                                            const double *__restrict__ b, double *out2,
                                                            double *partials, unsigned int *ticket) {
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiAccuracy e{b, x};
-  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  spmv_rows<L, TMA>(A, g, e, a0, a1);
   a0 = block_sum(a0, red);
   a1 = block_sum(a1, red);
   if (threadIdx.x == 0) {
@@ -220,12 +234,12 @@ __global__ void __launch_bounds__(kBlock) residual_kernel(CsrView A, const doubl
 }
 
 // y = A x (plain)
-template <int L>
-__global__ void __launch_bounds__(kBlock) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
+template <int L, bool TMA>
+__global__ void CGB_BOUNDS(TMA) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiStore e{y};
-  spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+  spmv_rows<L, TMA>(A, g, e, a0, a1);
 }
 
 } // namespace cgb

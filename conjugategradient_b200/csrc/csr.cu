@@ -5,6 +5,7 @@
 #include "launch.cuh"
 
 #include <cub/device/device_scan.cuh>
+#include <stdlib.h>
 
 using namespace cgb;
 
@@ -24,6 +25,22 @@ int csr_plan(cgb_csr *A) {
   if (need < A->grid_spmv) A->grid_spmv = (int)(need > 0 ? need : 1);
   const int64_t need_v = (A->n / 2 + kBlock - 1) / kBlock;
   if (need_v < A->grid_vec) A->grid_vec = (int)(need_v > 0 ? need_v : 1);
+  // TMA engine: a tile of 256 / L rows should carry about 7 * 256 non-zeros
+  int lt = 1;
+  while (lt < 32 && (double)lt * 7.0 < mean) lt <<= 1;
+  A->lanes_tma = lt;
+  const int tile_rows = kTmaConsumers / lt;
+  const size_t smem = tma_smem_bytes(tile_rows) + 1024;
+  int per_sm = (int)((size_t)227 * 1024 / smem);
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;
+  A->grid_tma = sms * per_sm;
+  const int64_t ntiles = (A->n + tile_rows - 1) / tile_rows;
+  if (ntiles < A->grid_tma) A->grid_tma = (int)(ntiles > 0 ? ntiles : 1);
+  // bulk copies need 16-byte aligned array bases; tiny systems gain nothing from staging
+  auto al16 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+  const char *env = getenv("CGB_SPMV_ENGINE"); // "vec" forces direct loads (A/B measurements)
+  A->use_tma = al16(A->vals) && al16(A->cols) && al16(A->rowptr) && ntiles >= 2 && !(env && !strcmp(env, "vec"));
   return CGB_OK;
 }
 
@@ -217,8 +234,10 @@ int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
   CGB_REQUIRE(ctx && A && d_x && d_y, "cgb_spmv: NULL argument");
   if (A->n == 0) return CGB_OK;
   ScopedDevice sd(ctx->device);
-  CsrView V{A->n, A->rowptr, A->cols, A->vals};
-  CGB_LAUNCH_L(A->lanes, spmv_kernel, A->grid_spmv, ctx->stream, V, d_x, d_y);
+  const SpmvLaunch lc = spmv_launch_cfg(A);
+  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+    launch_kernel(spmv_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_y);
+  });
   CGB_CUDA(cudaGetLastError());
   return CGB_OK;
 }
@@ -232,9 +251,12 @@ int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b,
     *xx = 0.0;
     return CGB_OK;
   }
-  CsrView V{A->n, A->rowptr, A->cols, A->vals};
   double *out2 = ctx->partials + 2 * kMaxPartials - 2; // tail of the scratch is never a partial slot
-  CGB_LAUNCH_L(A->lanes, residual_kernel, A->grid_spmv, ctx->stream, V, d_x, d_b, out2, ctx->partials, ctx->ticket);
+  const SpmvLaunch lc = spmv_launch_cfg(A);
+  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+    launch_kernel(residual_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_b, out2,
+                  ctx->partials, ctx->ticket);
+  });
   CGB_CUDA(cudaGetLastError());
   CGB_CUDA(cudaMemcpyAsync(ctx->pinned, out2, 2 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   CGB_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -177,10 +177,14 @@ int dist_enqueue_iteration(cgb_dist *d, double *x) {
   cgb_csr *A = d->Aloc;
   Workspace &w = A->ws;
   cudaStream_t s = d->ctx->stream;
-  CsrView V{A->n, A->rowptr, A->cols, A->vals};
+  const CsrView V = csr_view(A);
+  const SpmvLaunch lc = spmv_launch_cfg(A);
   cg_pupdate_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
   CGB_TRY(halo_exchange(d, w.p0, 1));
-  CGB_LAUNCH_LB(A->lanes, false, cg_spmv_kernel, A->grid_spmv, s, V, w.r, w.p0, w.p1, w.Ap, w.st, w.partials, d->scal + 0);
+  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+    launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
+                  w.p1, w.Ap, w.st, w.partials, d->scal + 0);
+  });
   CGB_TRY(halo_apply(d, w.Ap, w.p0, d->scal + 0, d->scal + 0, 1));
   CGB_NCCL(g_nccl.AllReduce(d->scal + 0, d->scal + 1, 1, ncclDouble, ncclSum, d->comm, s));
   cg_update_kernel<false><<<A->grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,

@@ -44,6 +44,9 @@ struct cgb_csr {
   int lanes = 8;       // lanes per row of the CSR kernel
   int grid_spmv = 0;   // CTAs for SpMV-shaped kernels
   int grid_vec = 0;    // CTAs for streaming vector kernels
+  bool use_tma = true; // TMA-staged row engine (spmv_tma.cuh) instead of direct loads
+  int lanes_tma = 1;   // lanes per row of the TMA engine (tile = 256 / lanes_tma rows)
+  int grid_tma = 0;
   // SELL-C-sigma shadow copy
   int sell_sigma = 0;
   int64_t sell_slices = 0;

@@ -1,0 +1,462 @@
+#!/usr/bin/env python
+"""bench.py — CG iterations/s on the reference's headline workload (BASELINE.json):
+3D 7-point Poisson 512^3, fp64 CSR, b = 1..n, x0 = 0, absolute tolerance 1e-8 * ||b||.
+
+  python bench.py --gpus 1 --steps K --warmup W          one B200
+  torchrun ... bench.py --gpus N ...                      row-partitioned over N B200 (strong scaling)
+  python bench.py --impl reference ...                    the reference's own CPU solver (oracle/_ref)
+
+A "step" is one full CG solve.  `value` = iterations / second with matrix and vectors resident in
+HBM; `e2e` = the same through the host-buffer C-ABI call (cgb_cg_solve_host: upload CSR + b from
+pinned host memory, solve, download x) inside the timed region.  One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cg_iterations_per_sec"
+UNIT = "iterations/s"
+WORKLOADS = {
+    # name: (stencil kind, m, rel tol)
+    "poisson3d_7pt_512": ("3d7", 512, 1e-8),   # BASELINE config C4 (north star)
+    "poisson3d_7pt_128": ("3d7", 128, 1e-8),   # C2
+    "stencil3d_27pt_256": ("3d27", 256, 1e-8), # C3
+    "poisson2d_5pt_128": ("2d5", 128, 1e-8),   # C1
+}
+
+
+def b_iter(n, nnz):
+    """Algorithmic bytes of one CG iteration."""
+    return 12 * nnz + 4 * (n + 1) + 88 * n
+
+
+def stencil_dims(kind, m):
+    from conjugategradient_b200 import generators as G
+    n = m * m if kind == "2d5" else m ** 3
+    return n, G.stencil_nnz(kind, m)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload):
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(workload)
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args, kind, m, rel):
+    """The reference's own CPU CG (unmodified sources + OpenMP SYCL stand-in, oracle/_ref) on the box's
+    host cores.  Each step is a bounded sample: the first `trips` iterations of the same system."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    from conjugategradient_b200 import generators as G
+    cfg_m = m
+    n, nnz = stencil_dims(kind, cfg_m)
+    t0 = time.time()
+    gen = {"3d7": G.poisson3d_7pt, "3d27": G.stencil3d_27pt, "2d5": G.poisson2d_5pt}[kind]
+    vals, cols, rows = gen_host_csr(kind, cfg_m)
+    b = G.default_rhs(n)
+    kind_ref = "reference" if oracle.have_ref("omp") else "port"
+    out = time_cpu(vals, cols, rows, b, target_seconds=args.cpu_seconds, steps=args.steps, warmup=args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": out["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": out["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": config_dict(args.workload, kind, cfg_m, n, nnz, rel, "cpu"),
+        "cpu_baseline": {"value": out["value"], "unit": UNIT, "cores": out["cores"], "kind": kind_ref,
+                         "sample": out["sample"]},
+        "e2e": {"value": out["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "setup_s": round(time.time() - t0, 1),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def gen_host_csr(kind, m):
+    """Host CSR of the stencil, built directly (no lexsort) so 512^3 takes seconds, not minutes."""
+    n = m * m if kind == "2d5" else m ** 3
+    if kind == "3d27" or m < 64:
+        from conjugategradient_b200 import generators as G
+        return {"3d7": G.poisson3d_7pt, "3d27": G.stencil3d_27pt, "2d5": G.poisson2d_5pt}[kind](m)
+    idx = np.arange(n, dtype=np.int64)
+    i, j = idx % m, (idx // m) % m
+    k = idx // (m * m)
+    offs = [(-m * m, k > 0), (-m, j > 0), (-1, i > 0), (0, None), (1, i < m - 1), (m, j < m - 1),
+            (m * m, k < (m - 1))] if kind == "3d7" else [(-m, j > 0), (-1, i > 0), (0, None), (1, i < m - 1), (m, j < m - 1)]
+    diag = 6.0 if kind == "3d7" else 4.0
+    cnt = np.zeros(n, dtype=np.int32)
+    for _, ok in offs:
+        cnt += 1 if ok is None else ok.astype(np.int32)
+    rows = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(cnt, out=rows[1:])
+    nnz = int(rows[-1])
+    cols = np.empty(nnz, dtype=np.int32)
+    vals = np.empty(nnz, dtype=np.float64)
+    pos = rows[:-1].copy()
+    for off, ok in offs:
+        sel = slice(None) if ok is None else ok
+        p = pos[sel]
+        cols[p] = (idx[sel] + off).astype(np.int32)
+        vals[p] = diag if off == 0 else -1.0
+        if ok is None:
+            pos += 1
+        else:
+            pos[ok] += 1
+    return vals, cols, rows.astype(np.int32)
+
+
+def time_cpu(vals, cols, rows, b, target_seconds, steps, warmup):
+    """Times the reference CPU solver on a bounded sample; returns iterations/s."""
+    import oracle
+    n = rows.size - 1
+    if oracle.have_ref("omp"):
+        ref = oracle.Ref("omp")
+        h = ref.cg_create(vals, cols, rows)
+        ncpu = os.cpu_count() or 1
+        # the fastest thread count among {all, 1/2, 1/4} of the host cores (oversubscribed hosts differ)
+        best_t, best_ms = None, None
+        for t in sorted({ncpu, max(1, ncpu // 2), max(1, ncpu // 4)}, reverse=True):
+            ref.set_threads(t)
+            ms = ref.cg_run(h, b, 0.0, trip_limit=2)["solve_ms"]
+            ms = min(ms, ref.cg_run(h, b, 0.0, trip_limit=2)["solve_ms"])
+            if best_ms is None or ms < best_ms:
+                best_t, best_ms = t, ms
+        ref.set_threads(best_t)
+        per_iter = max(best_ms / 2.0, 1e-3)
+        total_calls = max(1, steps + warmup)
+        trips = int(min(500, max(3, (target_seconds * 1e3 / total_calls) / per_iter)))
+        for _ in range(warmup):
+            ref.cg_run(h, b, 0.0, trip_limit=trips)
+        its, ms = 0, 0.0
+        for _ in range(steps):
+            r = ref.cg_run(h, b, 0.0, trip_limit=trips)
+            its += r["iterations"]
+            ms += r["solve_ms"]
+        ref.cg_destroy(h)
+        cores = best_t
+        what = "reference CG::solve (unmodified sources, OpenMP SYCL stand-in)"
+    else:
+        port = oracle.Port()
+        trips, cores = 5, 1
+        t0 = time.time()
+        its = port.cg_solve(vals, cols, rows, b, 0.0, max_iter=trips)["iterations"]
+        ms = (time.time() - t0) * 1e3
+        steps = 1
+        what = "C restatement oracle/cg_oracle.c (serial)"
+    return {"value": its / (ms / 1e3), "ms_per_step": ms / max(steps, 1), "cores": cores,
+            "sample": f"first {trips} CG iterations per step of the same system (n={n}), solve() timed as "
+                      f"test/Tester.cpp:43-46, {what}, {cores} threads"}
+
+
+def config_dict(workload, kind, m, n, nnz, rel, where, **extra):
+    d = {"workload": workload, "matrix": f"{kind} stencil m={m}", "n": n, "nnz": nnz, "format": "CSR fp64/int32",
+         "rhs": "b[i]=i+1, x0=0", "tolerance": f"absolute {rel:g}*||b||2 on the recurrence residual (reference stop rule)",
+         "step": "one full CG solve", "l2_policy": "inputs larger than L2 (CSR %.1f GB, vectors %.2f GB each)" %
+         ((12 * nnz + 4 * n) / 1e9, 8 * n / 1e9), "B_iter_bytes": b_iter(n, nnz), "where": where}
+    d.update(extra)
+    return d
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args, kind, m, rel):
+    from conjugategradient_b200 import _lib as L
+    from conjugategradient_b200 import generators as G
+    from conjugategradient_b200 import solver as S
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})")
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = S.Context(local_rank)
+    lib = ctx.lib
+    n, nnz = stencil_dims(kind, m)
+    mz = 1 if kind == "2d5" else m
+    plane = m if kind == "2d5" else m * m
+    planes = m
+    # contiguous slabs of grid planes per rank
+    row_starts = np.array([plane * ((planes * r) // world) for r in range(world + 1)], dtype=np.int64)
+    lo, hi = int(row_starts[rank]), int(row_starts[rank + 1])
+    nloc = hi - lo
+    A = S.Matrix.stencil(ctx, kind, m, 0 if kind == "2d5" else m, lo, hi)
+    b_host = np.arange(lo + 1, hi + 1, dtype=np.float64)
+    nb = float(np.sqrt(n * (n + 1) * (2 * n + 1) / 6.0))  # ||1..n||_2 in closed form
+    tol = rel * nb
+    bvec = S.Vector(ctx, b_host)
+    xvec = S.Vector(ctx, n=nloc)
+    opts = S.make_opts(time_kernels=1 if world == 1 else 0, check_every=args.check_every)
+    stats = L.CgStats()
+
+    dh = None
+    if world > 1:
+        import torch
+        idbuf = (C.c_ubyte * L.NCCL_ID_BYTES)()
+        if rank == 0:
+            L.check(lib.cgb_nccl_unique_id(idbuf))
+        t = torch.tensor(list(bytes(idbuf)), dtype=torch.uint8, device="cuda")
+        dist.broadcast(t, 0)
+        idbytes = bytes(t.cpu().tolist())
+        dh = C.c_void_p()
+        L.check(lib.cgb_dist_create(ctx.h, rank, world, idbytes, row_starts.ctypes.data_as(C.c_void_p), A.h, C.byref(dh)))
+
+    def solve_resident():
+        L.check(lib.cgb_memset(ctx.h, xvec.ptr, 0, 8 * nloc))
+        if dh is None:
+            L.check(lib.cgb_cg_solve(ctx.h, A.h, bvec.ptr, xvec.ptr, tol, -1, C.byref(opts), C.byref(stats)))
+        else:
+            L.check(lib.cgb_dist_cg_solve(dh, bvec.ptr, xvec.ptr, tol, -1, C.byref(opts), C.byref(stats)))
+        return stats.as_dict()
+
+    def barrier():
+        ctx.sync()
+        if dist is not None:
+            import torch
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def timed(fn, steps):
+        """K steps bracketed by barrier+sync, CUDA events on the library's stream, max over ranks."""
+        barrier()
+        e0, e1 = C.c_void_p(), C.c_void_p()
+        L.check(lib.cgb_event_record(ctx.h, C.byref(e0)))
+        outs = [fn() for _ in range(steps)]
+        L.check(lib.cgb_event_record(ctx.h, C.byref(e1)))
+        ms = C.c_double()
+        L.check(lib.cgb_event_elapsed_ms(e0, e1, C.byref(ms)))
+        barrier()
+        lib.cgb_event_destroy(e0)
+        lib.cgb_event_destroy(e1)
+        return max_over_ranks(ms.value), outs
+
+    # ---- device-resident solves -----------------------------------------------------------------
+    for _ in range(args.warmup):
+        solve_resident()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_total, outs = timed(solve_resident, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    iters = sum(o["iterations"] for o in outs)
+    value = iters / (ms_total / 1e3)
+    launches = sum_over_ranks(float(sum(o["kernel_launches"] for o in outs)))
+    last = outs[-1]
+    # true residual of the last solve (global)
+    rr, xx = C.c_double(), C.c_double()
+    if dh is None:
+        L.check(lib.cgb_residual(ctx.h, A.h, xvec.ptr, bvec.ptr, C.byref(rr), C.byref(xx)))
+    else:
+        L.check(lib.cgb_dist_residual(dh, xvec.ptr, bvec.ptr, C.byref(rr), C.byref(xx)))
+    true_rel = float(np.sqrt(rr.value)) / nb
+
+    # ---- roofline of the dominant kernel (SpMV + p.Ap), timed live with CUDA events ----------------
+    peak, peak_src = measured_peak()
+    roof = None
+    spmv = [o["spmv_ms"] for o in outs if o["timed_samples"] > 0]
+    if spmv:
+        k1_bytes = 12 * nnz + 4 * (n + 1) + 16 * n  # vals + cols + rowptr + p read + Ap write
+        k1_ms = float(np.mean(spmv))
+        ach = k1_bytes / (k1_ms * 1e6)
+        roof = {"bound": "hbm", "kernel": "cg_spmv_kernel (CSR SpMV + p.Ap, TMA-staged)", "achieved": ach, "peak": peak,
+                "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "traffic": ncu_traffic(args.workload),
+                "bytes_per_launch": k1_bytes, "ms_per_launch": k1_ms,
+                "share_of_iteration": k1_ms / (ms_total / max(iters, 1)),
+                "update_ms": float(np.mean([o["update_ms"] for o in outs])),
+                "pupdate_ms": float(np.mean([o["pupdate_ms"] for o in outs])),
+                "iteration_GBps_B_iter": iters * b_iter(n, nnz) / (ms_total * 1e6),
+                "iteration_frac_of_peak": iters * b_iter(n, nnz) / (ms_total * 1e6) / peak,
+                "iteration_frac_of_8TBps": iters * b_iter(n, nnz) / (ms_total * 1e6) / 8000.0}
+
+    # ---- end to end: host buffers in, host buffer out -----------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        hv, hc, hr = A.to_host()  # this rank's block (global columns), then pinned
+        nnz_loc = hv.size
+
+        def pinned(a):
+            p = C.c_void_p()
+            L.check(lib.cgb_host_alloc(a.nbytes, C.byref(p)))
+            out = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_ubyte)), shape=(a.nbytes,)).view(a.dtype)
+            out[...] = a
+            return out, p
+        pv, pv_h = pinned(hv)
+        pc, pc_h = pinned(hc)
+        pr, pr_h = pinned(hr)
+        pb, pb_h = pinned(b_host)
+        px, px_h = pinned(np.zeros(nloc))
+        del hv, hc, hr
+        e_opts = S.make_opts(check_every=args.check_every)
+        e_stats = L.CgStats()
+
+        def solve_e2e():
+            if dh is None:
+                L.check(lib.cgb_cg_solve_host(ctx.h, nloc, nnz_loc, pv.ctypes.data, pc.ctypes.data, pr.ctypes.data,
+                                              pb.ctypes.data, None, px.ctypes.data, tol, -1, C.byref(e_opts), C.byref(e_stats)))
+            else:
+                a2 = C.c_void_p()
+                L.check(lib.cgb_csr_create(ctx.h, nloc, nnz_loc, pv.ctypes.data, pc.ctypes.data, pr.ctypes.data, C.byref(a2)))
+                L.check(lib.cgb_dist_set_matrix(dh, row_starts.ctypes.data_as(C.c_void_p), a2))
+                lib.cgb_csr_destroy(a2)
+                L.check(lib.cgb_memcpy_h2d(ctx.h, bvec.ptr, pb.ctypes.data, 8 * nloc, 0))
+                L.check(lib.cgb_memset(ctx.h, xvec.ptr, 0, 8 * nloc))
+                L.check(lib.cgb_dist_cg_solve(dh, bvec.ptr, xvec.ptr, tol, -1, C.byref(e_opts), C.byref(e_stats)))
+                L.check(lib.cgb_memcpy_d2h(ctx.h, px.ctypes.data, xvec.ptr, 8 * nloc, 1))
+            return e_stats.as_dict()
+
+        if dh is None:
+            A.free()  # make room: the e2e path uploads its own copy every step
+        e_steps = max(1, min(args.steps, args.e2e_steps))
+        for _ in range(min(args.warmup, 1)):
+            solve_e2e()
+        e_ms, e_outs = timed(solve_e2e, e_steps)
+        e_iters = sum(o["iterations"] for o in e_outs)
+        h2d = sum_over_ranks(float(12 * nnz_loc + 4 * (nloc + 1) + 8 * nloc))
+        d2h = sum_over_ranks(float(8 * nloc))
+        e2e = {"value": e_iters / (e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "steps": e_steps, "ms_per_step": e_ms / e_steps,
+               "api": "cgb_cg_solve_host (pinned host CSR + b in, x out)" if dh is None else
+                      "cgb_csr_create + cgb_dist_set_matrix + cgb_dist_cg_solve + D2H per rank"}
+        x_host = np.array(px, copy=True)
+        for hnd in (pv_h, pc_h, pr_h, pb_h, px_h):
+            lib.cgb_host_free(hnd)
+        del pv, pc, pr, pb, px
+
+    # ---- CPU baseline: the reference's own solver on the host cores (N = 1, rank 0) ----------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        vals, cols, rows = gen_host_csr(kind, m)
+        b_full = G.default_rhs(n)
+        import oracle
+        out = time_cpu(vals, cols, rows, b_full, target_seconds=args.cpu_seconds, steps=1, warmup=0)
+        cpu = {"value": out["value"], "unit": UNIT, "cores": out["cores"],
+               "kind": "reference" if oracle.have_ref("omp") else "port", "sample": out["sample"]}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": config_dict(args.workload, kind, m, n, nnz, rel, f"{world}xB200",
+                                  parallelism=f"row-partitioned x{world}" if world > 1 else "single GPU",
+                                  iterations_per_solve=last["iterations"], true_rel_residual=true_rel,
+                                  loop="CUDA graph batches of %d iterations, device-side stop flag" % args.check_every),
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "achieved_GBps_B_iter": iters * b_iter(n, nnz) / (ms_total * 1e6),
+        }
+        print(json.dumps(line), flush=True)
+    if dh is not None:
+        lib.cgb_dist_destroy(dh)
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("CGB_BENCH_WORKLOAD", "poisson3d_7pt_512"), choices=sorted(WORKLOADS))
+    ap.add_argument("--m", type=int, default=int(os.environ.get("CGB_BENCH_M", "0")), help="override grid size (debug)")
+    ap.add_argument("--check-every", type=int, default=32)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    kind, m, rel = WORKLOADS[args.workload]
+    if args.m:
+        m = args.m
+    if args.impl == "reference":
+        run_reference(args, kind, m, rel)
+    else:
+        run_ours(args, kind, m, rel)
+
+
+if __name__ == "__main__":
+    main()

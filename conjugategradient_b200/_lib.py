@@ -60,6 +60,7 @@ SIGNATURES = {
     "cgb_memcpy_h2d": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t, C.c_int]),
     "cgb_memcpy_d2h": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t, C.c_int]),
     "cgb_memcpy_d2d": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t]),
+    "cgb_memcpy": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t, C.c_int]),
     "cgb_memset": (C.c_int, [c_vp, c_vp, C.c_int, C.c_size_t]),
     "cgb_fill_f64": (C.c_int, [c_vp, c_vp, C.c_double, C.c_size_t]),
     "cgb_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(c_vp)]),
@@ -103,6 +104,7 @@ SIGNATURES = {
     "cgb_mm_free": (C.c_int, [c_vp]),
     "cgb_nccl_unique_id": (C.c_int, [c_vp]),
     "cgb_dist_create": (C.c_int, [c_vp, C.c_int, C.c_int, c_vp, c_vp, c_vp, C.POINTER(c_vp)]),
+    "cgb_dist_set_matrix": (C.c_int, [c_vp, c_vp, c_vp]),
     "cgb_dist_destroy": (C.c_int, [c_vp]),
     "cgb_dist_cg_solve": (C.c_int, [c_vp, c_vp, c_vp, C.c_double, c_i64, C.POINTER(CgOpts), C.POINTER(CgStats)]),
     "cgb_dist_residual": (C.c_int, [c_vp, c_vp, c_vp, c_dp, c_dp]),

@@ -156,6 +156,17 @@ int cgb_memcpy_d2d(cgb_ctx *ctx, void *d_dst, const void *d_src, size_t bytes) {
   return CGB_OK;
 }
 
+int cgb_memcpy(cgb_ctx *ctx, void *dst, const void *src, size_t bytes, int sync) {
+  CGB_REQUIRE(ctx && (bytes == 0 || (dst && src)), "cgb_memcpy: NULL argument");
+  if (bytes == 0) return CGB_OK;
+  ScopedDevice sd(ctx->device);
+  CGB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
+  // pageable host memory may still be read after an async copy returns: callers that pass
+  // borrowed std::vector storage rely on the wait the reference issues next (src/CG.hpp:169)
+  if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CGB_OK;
+}
+
 int cgb_memset(cgb_ctx *ctx, void *d_ptr, int byte, size_t bytes) {
   CGB_REQUIRE(ctx && (bytes == 0 || d_ptr), "cgb_memset: NULL argument");
   if (bytes == 0) return CGB_OK;

@@ -368,18 +368,28 @@ int cgb_plan_halo(int rank, int nranks, const int64_t *row_starts, int64_t nnz_l
   return CGB_OK;
 }
 
-int cgb_dist_destroy(cgb_dist *d) {
-  if (!d) return CGB_OK;
-  ScopedDevice sd(d->ctx->device);
+static void dist_release_matrix(cgb_dist *d) {
   cudaStreamSynchronize(d->ctx->stream);
   if (d->comm_stream) cudaStreamSynchronize(d->comm_stream);
-  if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
   cgb_csr_destroy(d->Aloc);
   cgb_csr_destroy(d->Ahalo);
   cudaFree(d->halo_rows);
   cudaFree(d->send_idx);
   cudaFree(d->send_buf);
   cudaFree(d->halo);
+  d->Aloc = d->Ahalo = nullptr;
+  d->halo_rows = nullptr;
+  d->send_idx = nullptr;
+  d->send_buf = nullptr;
+  d->halo = nullptr;
+  d->nh = d->H = d->S = 0;
+}
+
+int cgb_dist_destroy(cgb_dist *d) {
+  if (!d) return CGB_OK;
+  ScopedDevice sd(d->ctx->device);
+  dist_release_matrix(d);
+  if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
   cudaFree(d->scal);
   if (d->ev_pack) cudaEventDestroy(d->ev_pack);
   if (d->ev_halo) cudaEventDestroy(d->ev_halo);

@@ -245,9 +245,21 @@ int cgb_dist_create(cgb_ctx *ctx, int rank, int nranks, const void *h_id128, con
   return CGB_OK;
 }
 
+int cgb_dist_set_matrix(cgb_dist *d, const int64_t *row_starts, cgb_csr *A) {
+  CGB_REQUIRE(d && row_starts && A, "cgb_dist_set_matrix: NULL argument");
+  CGB_REQUIRE(row_starts[d->rank + 1] - row_starts[d->rank] == A->n, "cgb_dist_set_matrix: row block size mismatch");
+  CGB_REQUIRE(row_starts[d->nranks] < ((int64_t)1 << 31), "cgb_dist_set_matrix: global size must fit 32-bit columns");
+  ScopedDevice sd(d->ctx->device);
+  dist_release_matrix(d);
+  d->n = A->n;
+  d->row_starts.assign(row_starts, row_starts + d->nranks + 1);
+  return dist_setup(d, A);
+}
+
 int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,
                       const cgb_cg_opts *opts_in, cgb_cg_stats *stats) {
   CGB_REQUIRE(d, "cgb_dist_cg_solve: handle is NULL");
+  if (!d->Aloc) return fail(CGB_ERR_STATE, "No Matrix given");
   if (!d_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");
   CGB_REQUIRE(d_x, "cgb_dist_cg_solve: x is NULL");
   cgb_cg_opts o;

@@ -64,6 +64,8 @@ int cgb_free(cgb_ctx *ctx, void *d_ptr);
 int cgb_memcpy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes, int sync);
 int cgb_memcpy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes, int sync);
 int cgb_memcpy_d2d(cgb_ctx *ctx, void *d_dst, const void *d_src, size_t bytes);
+/* Direction inferred from the pointers (unified addressing), like a SYCL USM queue.copy. */
+int cgb_memcpy(cgb_ctx *ctx, void *dst, const void *src, size_t bytes, int sync);
 int cgb_memset(cgb_ctx *ctx, void *d_ptr, int byte, size_t bytes);
 int cgb_fill_f64(cgb_ctx *ctx, double *d_ptr, double value, size_t n);
 /* Page-locked host staging (pinned H2D/D2H run at PCIe speed). */
@@ -207,6 +209,8 @@ int cgb_nccl_unique_id(void *h_id128);
 /* row_starts: nranks+1 global row offsets (same on every rank). */
 int cgb_dist_create(cgb_ctx *ctx, int rank, int nranks, const void *h_id128, const int64_t *row_starts,
                     cgb_csr *A_local_global_cols, cgb_dist **out);
+/* Replace the matrix of an existing handle (same communicator): re-runs the split and halo plan. */
+int cgb_dist_set_matrix(cgb_dist *d, const int64_t *row_starts, cgb_csr *A_local_global_cols);
 int cgb_dist_destroy(cgb_dist *d);
 /* d_b, d_x: local row block.  stats->iterations etc. are global (identical on all ranks). */
 int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,

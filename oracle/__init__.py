@@ -135,6 +135,12 @@ class Ref:
         L.ref_cg_solve.argtypes = [C.c_long, C.c_long, _dp, _ip, _ip, _dp, C.c_void_p, C.c_double, _dp,
                                    C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                    C.POINTER(C.c_long)]
+        L.ref_set_trip_limit.argtypes = [C.c_long]
+        L.ref_cg_create.argtypes = [C.c_long, C.c_long, _dp, _ip, _ip]
+        L.ref_cg_create.restype = C.c_void_p
+        L.ref_cg_run.argtypes = [C.c_void_p, _dp, C.c_double, C.c_long, C.c_void_p, C.POINTER(C.c_long),
+                                 C.POINTER(C.c_double)]
+        L.ref_cg_destroy.argtypes = [C.c_void_p]
         L.ref_cg_solve_missing.argtypes = [C.c_int, C.c_int, C.c_char_p, C.c_int]
         L.ref_reduce.argtypes = [C.c_int, C.c_long, _dp, C.c_void_p, C.c_double]
         L.ref_reduce.restype = C.c_double
@@ -149,8 +155,13 @@ class Ref:
     def threads(self):
         return int(self.lib.ref_num_threads())
 
-    def cg_solve(self, vals, cols, rows, b, tol, x0=None):
+    def set_threads(self, t):
+        self.lib.ref_set_threads(int(t))
+
+    def cg_solve(self, vals, cols, rows, b, tol, x0=None, trip_limit=0):
+        """trip_limit > 0 (bench timing samples only): leave the reference loop after that many trips."""
         n = len(rows) - 1
+        self.lib.ref_set_trip_limit(int(trip_limit))
         x = np.empty(n)
         it, foot = C.c_long(0), C.c_long(0)
         acc, ms = C.c_double(0), C.c_double(0)
@@ -161,6 +172,23 @@ class Ref:
         if rc != 0:
             raise RuntimeError(f"ref_cg_solve rc={rc}")
         return dict(x=x, iterations=int(it.value), accuracy=acc.value, solve_ms=ms.value, footprint=int(foot.value))
+
+    def cg_create(self, vals, cols, rows):
+        """Persistent reference solver (matrix set once) for timing loops; free with cg_destroy."""
+        return self.lib.ref_cg_create(len(rows) - 1, len(vals), _f64(vals), _i32(cols), _i32(rows))
+
+    def cg_run(self, handle, b, tol, trip_limit=0, want_x=False):
+        b = _f64(b)
+        x = np.empty(b.size) if want_x else None
+        it, ms = C.c_long(0), C.c_double(0)
+        rc = self.lib.ref_cg_run(handle, b, float(tol), int(trip_limit), None if x is None else x.ctypes.data,
+                                 C.byref(it), C.byref(ms))
+        if rc != 0:
+            raise RuntimeError(f"ref_cg_run rc={rc}")
+        return dict(x=x, iterations=int(it.value), solve_ms=ms.value)
+
+    def cg_destroy(self, handle):
+        self.lib.ref_cg_destroy(handle)
 
     def solve_missing(self, have_matrix, have_rhs):
         buf = C.create_string_buffer(256)

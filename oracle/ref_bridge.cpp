@@ -48,6 +48,18 @@ int ref_num_threads() {
 #endif
 }
 
+// Thread count of the OpenMP flavour (no-op for the serial one).
+void ref_set_threads(int t) {
+#ifdef STANDIN_OPENMP
+  if (t > 0) omp_set_num_threads(t);
+#else
+  (void)t;
+#endif
+}
+
+// Bounded timing samples: stop the reference loop after `trips` trips (0 = off). See the stand-in.
+void ref_set_trip_limit(long trips) { sy::standin_stats().trip_limit = trips; }
+
 // Whole solve through the reference's CG class, exactly as test/Tester.cpp:36-53 drives it.
 // iterations = number of AlphaCalculation submissions (one per loop trip, src/CG.hpp:385).
 int ref_cg_solve(long n, long nnz, const double *vals, const int *cols, const int *rows, const double *b,
@@ -85,6 +97,56 @@ int ref_cg_solve(long n, long nnz, const double *vals, const int *cols, const in
     return 1;
   }
 }
+
+// Persistent flavour for timing loops: the matrix is set once (setMatrix), every run sets b and a
+// zero initial guess and times solve() alone, exactly the region test/Tester.cpp:43-46 times.
+struct RefCG {
+  std::unique_ptr<CG<DT, Debuglevel::None>> cgp;
+  std::vector<DT> data;
+  std::vector<int> c, r;
+  long n;
+};
+void *ref_cg_create(long n, long nnz, const double *vals, const int *cols, const int *rows) {
+  auto *h = new RefCG;
+  h->n = n;
+  h->data.assign(vals, vals + nnz);
+  h->c.assign(cols, cols + nnz);
+  h->r.assign(rows, rows + n + 1);
+  h->cgp = CG<DT, Debuglevel::None>::createCG();
+  h->cgp->setMatrix(h->data, h->c, h->r);
+  // the host copies are only needed until the (synchronous) stand-in copy is done
+  std::vector<DT>().swap(h->data);
+  std::vector<int>().swap(h->c);
+  std::vector<int>().swap(h->r);
+  return h;
+}
+int ref_cg_run(void *handle, const double *b, double improvement, long trip_limit, double *x_out, long *iterations,
+               double *solve_ms) {
+  auto *h = static_cast<RefCG *>(handle);
+  try {
+    std::vector<DT> target(b, b + h->n), zeros(h->n, 0.0);
+    h->cgp->setTarget(target);
+    h->cgp->setInital(zeros);
+    sy::standin_stats().clear();
+    sy::standin_stats().trip_limit = trip_limit;
+    auto t0 = std::chrono::steady_clock::now();
+    h->cgp->solve(improvement);
+    auto t1 = std::chrono::steady_clock::now();
+    sy::standin_stats().trip_limit = 0;
+    if (iterations) *iterations = sy::standin_stats().count_containing("AlphaCalculation");
+    if (solve_ms) *solve_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    if (x_out) {
+      std::vector<DT> x;
+      h->cgp->extractTo(x);
+      std::memcpy(x_out, x.data(), sizeof(DT) * h->n);
+    }
+    return 0;
+  } catch (std::exception &e) {
+    std::fprintf(stderr, "ref_cg_run: %s\n", e.what());
+    return 1;
+  }
+}
+void ref_cg_destroy(void *handle) { delete static_cast<RefCG *>(handle); }
 
 // Error behaviour of solve() with missing inputs (src/CG.hpp:266-272): returns the what() text.
 int ref_cg_solve_missing(int have_matrix, int have_rhs, char *msg, int msg_len) {

@@ -44,7 +44,14 @@ namespace sycl {
 struct standin_stats_t {
   std::map<std::string, long> launches;
   long host_syncs = 0;
-  void clear() { launches.clear(); host_syncs = 0; }
+  // Bounded timing samples (bench.py only): after `trip_limit` BetaCalculation submissions — one per
+  // CG loop trip, reference src/CG.hpp:413 — the stand-in raises the host-visible stop flag the
+  // reference allocated with malloc_shared<bool> (src/CG.hpp:289), so the unmodified loop exits
+  // after exactly that many trips.  0 = off (the parity oracle never sets it).
+  long trip_limit = 0;
+  long trips = 0;
+  bool *shared_flag = nullptr;
+  void clear() { launches.clear(); host_syncs = 0; trips = 0; }
   long count_containing(const std::string &needle) const {
     long c = 0;
     for (auto &kv : launches)
@@ -66,6 +73,11 @@ template <class Name> inline void note_launch(const char *kind) {
   auto end = nm.find_first_of(";]");
   if (end != std::string::npos) nm = nm.substr(0, end);
   standin_stats().launches[std::string(kind) + ":" + nm]++;
+  if (nm.find("BetaCalculation") != std::string::npos) {
+    auto &st = standin_stats();
+    st.trips++;
+    if (st.trip_limit > 0 && st.trips >= st.trip_limit && st.shared_flag) *st.shared_flag = true;
+  }
 }
 } // namespace detail
 
@@ -351,12 +363,17 @@ template <class T> T *malloc_device(std::size_t n, const queue &) {
   return static_cast<T *>(std::malloc(n * sizeof(T) > 0 ? n * sizeof(T) : 1));
 }
 template <class T> T *malloc_shared(std::size_t n, const queue &) {
-  return static_cast<T *>(std::malloc(n * sizeof(T) > 0 ? n * sizeof(T) : 1));
+  T *p = static_cast<T *>(std::malloc(n * sizeof(T) > 0 ? n * sizeof(T) : 1));
+  if constexpr (std::is_same<T, bool>::value) standin_stats().shared_flag = p;
+  return p;
 }
 template <class T> T *malloc_host(std::size_t n, const queue &) {
   return static_cast<T *>(std::malloc(n * sizeof(T) > 0 ? n * sizeof(T) : 1));
 }
-inline void free(void *p, const queue &) { std::free(p); }
+inline void free(void *p, const queue &) {
+  if (p == static_cast<void *>(standin_stats().shared_flag)) standin_stats().shared_flag = nullptr;
+  std::free(p);
+}
 
 using std::sqrt;
 using std::fabs;

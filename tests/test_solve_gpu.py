@@ -96,14 +96,18 @@ def test_solve_vs_oracle(ctx, port, name, fused):
     nb = np.linalg.norm(b)
     res_g = np.linalg.norm(b - port.spmv(v, c, r, x)) / nb
     res_o = np.linalg.norm(b - port.spmv(v, c, r, o["x"])) / nb
-    assert abs(res_g - res_o) <= 1e-10
+    if name.startswith("rspd"):
+        # different trip counts (see above) stop on different residuals; both must have reached the tolerance
+        assert res_g <= 3 * rel and res_o <= 3 * rel
+    else:
+        assert abs(res_g - res_o) <= 1e-10
     # r.r history follows the oracle's while the residual is well above rounding level
     h = cg.history()
     assert h.size == st["iterations"] + 1
     k = min(h.size, o["hist"].size, 25)
     assert np.allclose(h[:k], o["hist"][:k], rtol=1e-8, atol=0)
-    # b - Ax cancels ~8 digits at this tolerance, so the two summation orders agree to ~1e-8 only
-    assert abs(cg.accuracy() - port.accuracy(v, c, r, x, b)[0]) <= 1e-6 * cg.accuracy()
+    # b - Ax cancels -log10(rel) digits at this tolerance, so the two summation orders agree to ~1e-16/rel only
+    assert abs(cg.accuracy() - port.accuracy(v, c, r, x, b)[0]) <= (1e-14 / rel) * cg.accuracy()
     if name == "C1_p2d_128":
         assert o["iterations"] == 366  # SURVEY.md §8c probe
 

@@ -16,6 +16,7 @@ struct LoopCfg {
   bool time_kernels;
   SpmvLaunch sl;
   int grid_vec;
+  int grid_pup;
 };
 
 // Enqueue one CG iteration on `s`.  When `timed`, bracket the kernels with external event records
@@ -27,25 +28,21 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
     return timed ? cudaEventRecordWithFlags(w.ev[i], s, cudaEventRecordExternal) : cudaSuccess;
   };
   CGB_CUDA(mark(0));
-  if (!c.fused) cg_pupdate_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
+  if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_CUDA(mark(1));
   dispatch_lanes(c.sl.lanes, c.sl.tma, [&](auto Lc, auto Tc) {
     constexpr int L = decltype(Lc)::value;
     constexpr bool T = decltype(Tc)::value;
     if (c.fused)
-      launch_kernel(cg_spmv_kernel<L, T, true>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
+      launch_kernel(cg_spmv_kernel<L, T, true>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, x, w.st, w.partials,
                     (double *)nullptr);
     else
-      launch_kernel(cg_spmv_kernel<L, T, false>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, w.st, w.partials,
+      launch_kernel(cg_spmv_kernel<L, T, false>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, x, w.st, w.partials,
                     (double *)nullptr);
   });
   CGB_CUDA(mark(2));
-  if (c.fused)
-    cg_update_kernel<true><<<c.grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
-                                                          (const double *)nullptr, (double *)nullptr);
-  else
-    cg_update_kernel<false><<<c.grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
-                                                           (const double *)nullptr, (double *)nullptr);
+  cg_update_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, (const double *)nullptr,
+                                                 (double *)nullptr);
   CGB_CUDA(mark(3));
   CGB_CUDA(cudaGetLastError());
   return CGB_OK;
@@ -116,7 +113,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
-  LoopCfg cfg{fused, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec};
+  LoopCfg cfg{fused, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup};
   if (cfg.time_kernels)
     for (auto &e : w.ev)
       if (!e) CGB_CUDA(cudaEventCreate(&e));
@@ -209,7 +206,10 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     if (h.done || h.iter >= h.max_iter) finished = true;
     slot ^= 1;
   }
-  // drain whatever was issued ahead and take the final state
+  // the x update of the last trip (deferred: see cg_kernels.cuh), then drain and take the final state
+  cg_xflush_kernel<<<cfg.grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, fused ? 1 : 0, w.st);
+  CGB_CUDA(cudaGetLastError());
+  launches += 1;
   CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
   CGB_CUDA(cudaEventRecord(t1, s));
   CGB_CUDA(cudaEventSynchronize(t1));

@@ -1,12 +1,19 @@
 // cg_kernels.cuh — the kernels of one CG iteration (reference loop: src/CG.hpp:359-436).
 //
 //   K0  cg_init_kernel      r = b - A x0, rr = r.r                       (:314-341)
-//   K3  cg_pupdate_kernel   p = r + beta p     (only when not fused)      (:418)
+//   K3  cg_pupdate_kernel   x += alpha_prev p_old ; p = r + beta p_old   (only when not fused)   (:390, :418)
 //   K1  cg_spmv_kernel      Ap = A p, pAp = p.Ap, alpha = rr / pAp        (:374-386)
-//       fused flavour: p = r + beta p_old is formed in the gather and written once
-//   K2  cg_update_kernel    x += alpha p, r -= alpha Ap, rr' = r.r,       (:390-416)
+//       fused flavour: p = r + beta p_old is formed in the gather and written once, and the
+//       deferred x += alpha_prev p_old rides on the same row-aligned read of p_old
+//   K2  cg_update_kernel    r -= alpha Ap, rr' = r.r,                     (:392-416)
 //                           stop test on the OLD rr, beta = rr'/rr, rr = rr', ++iter
+//   KX  cg_xflush_kernel    x += alpha p for the last trip (once, after the loop)   (:390)
 //   K4  residual_kernel     sum (b - A x)^2, sum x^2                      (:477-499)
+//
+// Deferred x update: the reference applies x += alpha_k p_k inside trip k (:390).  x is never read
+// inside the loop, so the same fma is applied one kernel later, where p_k is read anyway (the next
+// p-update), and once more after the loop for the last trip.  Same operands, same rounding, one
+// vector read fewer per iteration (the K2 pass no longer touches x or p).
 //
 // Every kernel is gated on the device-side state (no host round trip per iteration): once the
 // stop test has fired or the trip cap is reached, later launches return immediately, so a CUDA
@@ -72,29 +79,40 @@ __global__ void CGB_BOUNDS(TMA) cg_init_kernel(CsrView A, const double *__restri
 
 // ---- K3 (unfused only) -------------------------------------------------------------------------
 static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, const double *__restrict__ r,
-                                                             double *__restrict__ p, const CgState *st) {
+                                                             double *__restrict__ p, double *__restrict__ x,
+                                                             const CgState *st) {
   if (!cg_active(st)) return;
   const double beta = st->beta;
+  const double alpha = st->alpha; // of the previous trip (0 before the first: p is zero then)
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   const int64_t n2 = n >> 1;
   const double2 *r2 = reinterpret_cast<const double2 *>(r);
   double2 *p2 = reinterpret_cast<double2 *>(p);
+  double2 *x2 = reinterpret_cast<double2 *>(x);
   for (int64_t i = tid; i < n2; i += nthr) {
     const double2 rv = r2[i];
     double2 pv = p2[i];
+    double2 xv = x2[i];
+    xv.x = fma(alpha, pv.x, xv.x);
+    xv.y = fma(alpha, pv.y, xv.y);
     pv.x = fma(beta, pv.x, rv.x);
     pv.y = fma(beta, pv.y, rv.y);
+    x2[i] = xv;
     p2[i] = pv;
   }
-  if ((n & 1) && tid == 0) p[n - 1] = fma(beta, p[n - 1], r[n - 1]);
+  if ((n & 1) && tid == 0) {
+    const double po = p[n - 1];
+    x[n - 1] = fma(alpha, po, x[n - 1]);
+    p[n - 1] = fma(beta, po, r[n - 1]);
+  }
 }
 
 // ---- K1 -------------------------------------------------------------------------------------
 // FUSED: p buffers ping-pong on the iteration parity; p_old = pbuf[iter & 1], p_new = pbuf[~iter & 1].
 template <int L, bool TMA, bool FUSED>
 __global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
-                                                          double *pbuf1, double *__restrict__ Ap, CgState *st,
-                                                          double *partials, double *local_out) {
+                                                          double *pbuf1, double *__restrict__ Ap, double *x,
+                                                          CgState *st, double *partials, double *local_out) {
   if (!cg_active(st)) return;
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
@@ -104,7 +122,7 @@ __global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restri
     double *p_new = odd ? pbuf0 : pbuf1;
     const double beta = st->beta;
     GatherFusedP g{r, p_old, beta};
-    EpiDotFusedP e{Ap, r, p_old, p_new, beta};
+    EpiDotFusedP e{Ap, r, p_old, p_new, x, beta, st->alpha};
     spmv_rows<L, TMA>(A, g, e, a0, a1);
   } else {
     GatherPlain g{pbuf0};
@@ -128,43 +146,33 @@ __global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restri
 
 // ---- K2 -------------------------------------------------------------------------------------
 // Single GPU (pAp_in == NULL, local_out == NULL): alpha comes from the state and the last CTA advances
-// the state.  Multi-GPU: alpha = rr / *pAp_in (the all-reduced p.Ap), the local r.r partial goes to
-// *local_out and cg_advance_kernel advances the state after the second all-reduce.
-template <bool FUSED>
-__global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__restrict__ x, const double *pbuf0,
-                                                            const double *pbuf1, double *__restrict__ r,
+// the state.  Multi-GPU: alpha = rr / *pAp_in (the all-reduced p.Ap) is also stored to the state for
+// the deferred x update, the local r.r partial goes to *local_out and cg_advance_kernel advances the
+// state after the second all-reduce.
+static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__restrict__ r,
                                                             const double *__restrict__ Ap, CgState *st,
-                                                            double *partials, double *hist,
-                                                            const double *pAp_in, double *local_out) {
+                                                            double *partials, double *hist, const double *pAp_in,
+                                                            double *local_out) {
   if (!cg_active(st)) return;
   __shared__ double red[32];
   const double alpha = pAp_in ? st->rr / *pAp_in : st->alpha;
-  // fused flavour: this iteration's p is the buffer K1 just wrote
-  const double *p = FUSED ? (((st->iter & 1) != 0) ? pbuf0 : pbuf1) : pbuf0;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   const int64_t n2 = n >> 1;
-  double2 *x2 = reinterpret_cast<double2 *>(x);
   double2 *r2 = reinterpret_cast<double2 *>(r);
-  const double2 *p2 = reinterpret_cast<const double2 *>(p);
   const double2 *q2 = reinterpret_cast<const double2 *>(Ap);
   double acc = 0.0;
   for (int64_t i = tid; i < n2; i += nthr) {
-    double2 xv = x2[i], rv = r2[i];
-    const double2 pv = p2[i], qv = q2[i];
-    xv.x = fma(alpha, pv.x, xv.x);
-    xv.y = fma(alpha, pv.y, xv.y);
+    double2 rv = r2[i];
+    const double2 qv = q2[i];
     rv.x = fma(-alpha, qv.x, rv.x);
     rv.y = fma(-alpha, qv.y, rv.y);
-    x2[i] = xv;
     r2[i] = rv;
     acc = fma(rv.x, rv.x, acc);
     acc = fma(rv.y, rv.y, acc);
   }
   if ((n & 1) && tid == 0) {
-    const int64_t i = n - 1;
-    x[i] = fma(alpha, p[i], x[i]);
-    const double rv = fma(-alpha, Ap[i], r[i]);
-    r[i] = rv;
+    const double rv = fma(-alpha, Ap[n - 1], r[n - 1]);
+    r[n - 1] = rv;
     acc = fma(rv, rv, acc);
   }
   acc = block_sum(acc, red);
@@ -185,10 +193,34 @@ __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__
         st->iter = it;
         if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
       } else {
+        st->alpha = alpha; // every CTA used this value; kept for the deferred x update
         *local_out = rr_new;
       }
     }
   }
+}
+
+// ---- KX -------------------------------------------------------------------------------------
+// The x update of the LAST trip (the ones before it were applied by the following p-update).
+// Launched once after the loop; p of the last trip is pbuf0 (unfused) or the buffer the parity
+// of the trip counter selects (fused).
+static __global__ void __launch_bounds__(kBlock) cg_xflush_kernel(int64_t n, double *__restrict__ x, const double *pbuf0,
+                                                            const double *pbuf1, int fused, const CgState *st) {
+  if (st->iter <= 0) return; // no trip ran: nothing pending
+  const double alpha = st->alpha;
+  const double *p = (fused && (st->iter & 1)) ? pbuf1 : pbuf0;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  double2 *x2 = reinterpret_cast<double2 *>(x);
+  const double2 *p2 = reinterpret_cast<const double2 *>(p);
+  for (int64_t i = tid; i < n2; i += nthr) {
+    double2 xv = x2[i];
+    const double2 pv = p2[i];
+    xv.x = fma(alpha, pv.x, xv.x);
+    xv.y = fma(alpha, pv.y, xv.y);
+    x2[i] = xv;
+  }
+  if ((n & 1) && tid == 0) x[n - 1] = fma(alpha, p[n - 1], x[n - 1]);
 }
 
 // Multi-GPU: advance the state from the all-reduced scalars (one thread).

@@ -18,13 +18,22 @@ int csr_plan(cgb_csr *A) {
   A->lanes = lanes;
   const int sms = A->ctx->sm_count;
   A->grid_spmv = sms * 8;
-  A->grid_vec = sms * 8;
+  // streaming vector kernels: exactly one resident wave (grid-stride loops), so no partial second wave
+  // leaves SMs idle at the tail; CGB_VEC_CTAS caps the CTAs per SM for A/B measurements
+  int occ_u = 8, occ_p = 8;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_u, cg_update_kernel, kBlock, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, cg_pupdate_kernel, kBlock, 0);
+  int cap = 8;
+  if (const char *e = getenv("CGB_VEC_CTAS")) cap = atoi(e) > 0 ? atoi(e) : cap;
+  A->grid_vec = sms * (occ_u < cap ? (occ_u > 0 ? occ_u : 1) : cap);
+  A->grid_pup = sms * (occ_p < cap ? (occ_p > 0 ? occ_p : 1) : cap);
   // never launch more CTAs than there is work for
   const int64_t rows_per_cta = (int64_t)(kBlock / lanes) * 2;
   const int64_t need = (A->n + rows_per_cta - 1) / rows_per_cta;
   if (need < A->grid_spmv) A->grid_spmv = (int)(need > 0 ? need : 1);
   const int64_t need_v = (A->n / 2 + kBlock - 1) / kBlock;
   if (need_v < A->grid_vec) A->grid_vec = (int)(need_v > 0 ? need_v : 1);
+  if (need_v < A->grid_pup) A->grid_pup = (int)(need_v > 0 ? need_v : 1);
   // TMA engine: a tile of 256 / L rows should carry about 7 * 256 non-zeros
   int lt = 1;
   while (lt < 32 && (double)lt * 7.0 < mean) lt <<= 1;

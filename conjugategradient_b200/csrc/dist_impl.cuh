@@ -179,16 +179,15 @@ int dist_enqueue_iteration(cgb_dist *d, double *x) {
   cudaStream_t s = d->ctx->stream;
   const CsrView V = csr_view(A);
   const SpmvLaunch lc = spmv_launch_cfg(A);
-  cg_pupdate_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.p0, w.st);
+  cg_pupdate_kernel<<<A->grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_TRY(halo_exchange(d, w.p0, 1));
   dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
     launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
-                  w.p1, w.Ap, w.st, w.partials, d->scal + 0);
+                  w.p1, w.Ap, x, w.st, w.partials, d->scal + 0);
   });
   CGB_TRY(halo_apply(d, w.Ap, w.p0, d->scal + 0, d->scal + 0, 1));
   CGB_NCCL(g_nccl.AllReduce(d->scal + 0, d->scal + 1, 1, ncclDouble, ncclSum, d->comm, s));
-  cg_update_kernel<false><<<A->grid_vec, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, w.r, w.Ap, w.st, w.partials, w.hist,
-                                                         d->scal + 1, d->scal + 2);
+  cg_update_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, d->scal + 1, d->scal + 2);
   CGB_NCCL(g_nccl.AllReduce(d->scal + 2, d->scal + 3, 1, ncclDouble, ncclSum, d->comm, s));
   cg_advance_kernel<<<1, 32, 0, s>>>(w.st, d->scal + 3, w.hist);
   CGB_CUDA(cudaGetLastError());
@@ -343,6 +342,9 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     CGB_CUDA(cudaStreamSynchronize(s));
     if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter) break;
   }
+  if (n > 0) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st); // last trip's x update
+  CGB_CUDA(cudaGetLastError());
+  launches += 1;
   CGB_CUDA(cudaEventRecord(t1, s));
   CGB_CUDA(cudaEventSynchronize(t1));
   const CgState &f = w.h_st[0];

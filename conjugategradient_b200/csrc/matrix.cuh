@@ -43,7 +43,8 @@ struct cgb_csr {
   // plan
   int lanes = 8;       // lanes per row of the CSR kernel
   int grid_spmv = 0;   // CTAs for SpMV-shaped kernels
-  int grid_vec = 0;    // CTAs for streaming vector kernels
+  int grid_vec = 0;    // CTAs for the x/r update (+ r.r) kernel: one resident wave
+  int grid_pup = 0;    // CTAs for the p-update / x-flush kernels: one resident wave
   bool use_tma = true; // TMA-staged row engine (spmv_tma.cuh) instead of direct loads
   int lanes_tma = 1;   // lanes per row of the TMA engine (tile = 256 / lanes_tma rows)
   int grid_tma = 0;

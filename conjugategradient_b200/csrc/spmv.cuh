@@ -41,15 +41,20 @@ struct EpiDotP { // Ap[i] = s ; acc0 += p[i] * s
     a0 += p[i] * s;
   }
 };
-struct EpiDotFusedP { // p_new[i] = r[i] + beta p_old[i] ; Ap[i] = s ; acc0 += p_new[i] * s
+// x[i] += alpha_prev p_old[i] (deferred) ; p_new[i] = r[i] + beta p_old[i] ; Ap[i] = s ; acc0 += p_new[i] * s
+struct EpiDotFusedP {
   static constexpr int NRED = 1;
   double *y;
   const double *r;
   const double *p_old;
   double *p_new;
+  double *x;
   double beta;
+  double alpha_prev;
   __device__ __forceinline__ void row(int64_t i, double s, double &a0, double &) const {
-    const double pn = fma(beta, p_old[i], r[i]);
+    const double po = p_old[i];
+    x[i] = fma(alpha_prev, po, x[i]);
+    const double pn = fma(beta, po, r[i]);
     p_new[i] = pn;
     y[i] = s;
     a0 += pn * s;

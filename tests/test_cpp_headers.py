@@ -1,0 +1,127 @@
+"""The drop-in C++ headers (include/CG.hpp, LinearAlgebraTypes.hpp, VectorOperations.hpp, utils.hpp):
+CPU: they compile (our drivers, and the reference's unmodified test/Tester.cpp where the reference
+tree is present) and a driver without a GPU fails loudly.  GPU: the drivers' results match the
+oracle (the reference's own Tester built against the SYCL stand-in, and NumPy for the exact ops)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conjugategradient_b200 import generators as G
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EX = os.path.join(ROOT, "examples")
+TESTER = os.path.join(EX, "tester")
+OPS = os.path.join(EX, "ops_demo")
+UNMOD = os.path.join(EX, "_ref", "tester_unmodified")
+
+
+def _built():
+    if not (os.path.exists(TESTER) and os.path.exists(OPS)):
+        subprocess.run(["make", "-C", EX, "-s"], check=True)
+    return True
+
+
+def test_headers_compile_and_link():
+    assert _built()
+    assert os.access(TESTER, os.X_OK) and os.access(OPS, os.X_OK)
+    if os.path.exists("/root/reference/test/Tester.cpp"):
+        assert os.access(UNMOD, os.X_OK)  # the reference's own driver against our headers, zero edits
+
+
+def test_header_api_surface():
+    """Every public name of the reference headers exists in ours."""
+    cg = open(os.path.join(ROOT, "include", "CG.hpp")).read()
+    for name in ["createCG", "setMatrix", "getDimension", "setTarget", "setInital", "setInitial",
+                 "calculateExpectedStepCount", "solve", "accuracy", "extract", "extractTo", "memoryFootprint",
+                 "No right hand side to solve for", "No Matrix given"]:
+        assert name in cg, name
+    vo = open(os.path.join(ROOT, "include", "VectorOperations.hpp")).read()
+    for name in ["setVectorSize", "dot_product_optimised", "dot_product_trivial", "dot_product(", "norm", "saxpby",
+                 "sambx", "sapbx", "spmv"]:
+        assert name in vo, name
+    la = open(os.path.join(ROOT, "include", "LinearAlgebraTypes.hpp")).read()
+    for name in ["enum Debuglevel", "struct Asycl_deleter", "class Matrix", "class Vector", "class Scalar", "data_ptr",
+                 "columns_ptr", "rows_ptr", "init_empty", "operator DT *"]:
+        assert name in la, name
+
+
+def test_driver_without_gpu_fails_loudly(tmp_path):
+    from conjugategradient_b200 import _lib as L
+    if L.load().cgb_device_count() > 0:
+        pytest.skip("GPU present")
+    _built()
+    v, c, r = G.poisson2d_5pt(4)
+    p = str(tmp_path / "a.mtx")
+    G.write_mtx_reference_dialect(p, v, c, r)
+    out = subprocess.run([TESTER, p], capture_output=True, text=True)
+    assert out.returncode != 0 and "no CPU fallback" in out.stderr
+
+
+# ---- GPU ----------------------------------------------------------------------------------------
+def _expected_ops(n, m):
+    i = np.arange(n)
+    x = ((i % 17) - 8.0) * 0.125
+    y = (((i * 7) % 13) - 6.0) * 0.25
+    d = float(np.dot(x, y))
+    exp = {"dot_trivial": 2.5 + d, "dot_optimised": 2.5 + 2 * d, "dot_product": 2.5 + 3 * d, "norm": float(np.dot(x, x)),
+           "saxpby": float((0.5 * x - 2.0 * y).sum()), "sapbx": float((x - 2.0 * y).sum()),
+           "sambx_inplace": float((x + 2.0 * y).sum())}
+    v, c, r = G.poisson2d_5pt(m)
+    N = m * m
+    vec = ((np.arange(N) * 5) % 11) - 5.0
+    av = np.array([np.dot(v[r[k]:r[k + 1]], vec[c[r[k]:r[k + 1]]]) for k in range(N)])
+    exp["spmv"] = (N, v.size, float(np.dot(av, np.arange(N) % 7)), float(np.dot(av, av)))
+    return exp
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,m", [(1000, 16), (1, 2), (100003, 33)])
+def test_ops_demo_exact(n, m):
+    _built()
+    out = subprocess.run([OPS, str(n), str(m)], capture_output=True, text=True, check=True).stdout
+    got = {ln.split()[0]: ln.split()[1:] for ln in out.splitlines()}
+    exp = _expected_ops(n, m)
+    for k in ["dot_trivial", "dot_optimised", "dot_product", "norm", "saxpby", "sapbx", "sambx_inplace"]:
+        assert float(got[k][0]) == exp[k], k          # dyadic inputs: exact whatever the summation order
+    N, nnz, s1, s2 = exp["spmv"]
+    assert (int(got["spmv"][0]), int(got["spmv"][1]), float(got["spmv"][2]), float(got["spmv"][3])) == (N, nnz, s1, s2)
+    assert " ".join(got["missing"]) == "No right hand side to solve for"
+    dim, iters, conv, acc, foot = got["solve"]
+    assert int(dim) == N and int(conv) == 1 and 1 <= int(iters) <= N + 1
+    assert int(foot) == (2 * nnz + 4 * N) * 8 + 2 * N * 4      # reference src/CG.hpp:555-558
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("binary", ["tester", "tester_unmodified"])
+def test_tester_matches_reference_tester(tmp_path, binary):
+    """Same .mtx through the reference's own Tester (CPU, SYCL stand-in) and through the same driver
+    source built against our headers: identical dim / NNZ, accuracy at rounding level on both."""
+    _built()
+    exe = TESTER if binary == "tester" else UNMOD
+    if not os.path.exists(exe):
+        pytest.skip("reference tree was not present at build time")
+    v, c, r = G.poisson2d_5pt(24)
+    p = str(tmp_path / "p.mtx")
+    G.write_mtx_reference_dialect(p, v, c, r)
+    ours = subprocess.run([exe, p], capture_output=True, text=True, check=True)
+    dim, nnz, ms, acc = ours.stdout.split()
+    assert int(dim) == 576 and int(nnz) == v.size and float(ms) > 0
+    assert float(acc) < 1e-24                              # Tester's 1e-24 tolerance drives |b-Ax|^2/|x|^2 to rounding level
+    ref_exe = os.path.join(ROOT, "oracle", "_ref", "tester_serial")
+    if os.path.exists(ref_exe):
+        ref = subprocess.run([ref_exe, p], capture_output=True, text=True, check=True).stdout.split()
+        assert ref[0] == dim and ref[1] == nnz and float(ref[3]) < 1e-24
+
+
+@pytest.mark.gpu
+def test_tester_rel_tolerance_iterations(tmp_path, port):
+    _built()
+    v, c, r = G.poisson2d_5pt(128)                           # BASELINE config C1 through the .mtx path
+    p = str(tmp_path / "c1.mtx")
+    G.write_mtx_reference_dialect(p, v, c, r)
+    out = subprocess.run([TESTER, p, "rel:1e-8"], capture_output=True, text=True, check=True)
+    info = out.stderr.split()
+    iters = int(info[info.index("iterations") + 1])
+    assert abs(iters - 366) <= 7                             # SURVEY.md §8c probe: 366 (+-2 %)

@@ -20,8 +20,10 @@ def main():
             A = S.Matrix.stencil(ctx, kind, m)
             n, nnz = A.N(), A.NNZ()
             b = G.default_rhs(n)
-            for fused in (0, 1):
-                for timed in (0, 1):
+            fl = [int(c) for c in os.environ.get("PROBE_FUSED", "01")]
+            tl = [int(c) for c in os.environ.get("PROBE_TIMED", "01")]
+            for fused in fl:
+                for timed in tl:
                     cg = S.CG(ctx, fuse_p_update=fused, time_kernels=timed, check_every=25)
                     cg.setMatrix(A)
                     cg.setTarget(b)
@@ -34,9 +36,9 @@ def main():
                     line = (f"{kind} m={m} n={n} nnz={nnz} fused={fused} timed={timed} it={it} {it / sec:9.1f} it/s "
                             f"{it * B_iter / sec / 1e9:8.1f} GB/s(B_iter)")
                     if timed:
-                        k1 = (12 * nnz + 4 * (n + 1) + 16 * n) / (st["spmv_ms"] * 1e6) if st["spmv_ms"] else 0
-                        k2 = 48 * n / (st["update_ms"] * 1e6) if st["update_ms"] else 0
-                        k3 = 24 * n / (st["pupdate_ms"] * 1e6) if st["pupdate_ms"] else 0
+                        k1 = (12 * nnz + 4 * (n + 1) + (48 if fused else 16) * n) / (st["spmv_ms"] * 1e6) if st["spmv_ms"] else 0
+                        k2 = 24 * n / (st["update_ms"] * 1e6) if st["update_ms"] else 0
+                        k3 = 40 * n / (st["pupdate_ms"] * 1e6) if st["pupdate_ms"] else 0
                         line += (f" | spmv {st['spmv_ms']:.4f} ms {k1:7.1f} GB/s | update {st['update_ms']:.4f} ms {k2:7.1f} GB/s"
                                  f" | pupd {st['pupdate_ms']:.4f} ms {k3:7.1f} GB/s | samples {st['timed_samples']}")
                     print(line, flush=True)

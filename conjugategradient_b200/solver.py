@@ -323,3 +323,87 @@ def mm_read(path: str):
     finally:
         lib.cgb_mm_free(h)
     return vals, cols, rows
+
+
+# ---- row-partitioned multi-GPU (one process per GPU; new) ---------------------------
+def partition_rows(n: int, world: int, align: int = 1, rowptr=None) -> np.ndarray:
+    """world+1 global row offsets of contiguous row blocks.  Balanced by rows (multiples of `align`,
+    e.g. one grid plane for a stencil) or, when `rowptr` is given, by non-zeros."""
+    if rowptr is not None:
+        rp = np.asarray(rowptr, dtype=np.int64)
+        targets = rp[-1] * np.arange(1, world, dtype=np.float64) / world
+        cuts = np.searchsorted(rp, targets, side="left")
+        starts = np.concatenate([[0], cuts, [n]]).astype(np.int64)
+        return np.maximum.accumulate(starts)
+    units = n // align
+    starts = np.array([align * ((units * r) // world) for r in range(world + 1)], dtype=np.int64)
+    starts[-1] = n
+    return starts
+
+
+def local_block(vals, cols, rows, lo: int, hi: int):
+    """Rows [lo, hi) of a host CSR matrix with GLOBAL column indices (what cgb_dist_create takes)."""
+    rows = np.asarray(rows)
+    a, b = int(rows[lo]), int(rows[hi])
+    return _f64(vals[a:b]), _i32(cols[a:b]), _i32(rows[lo:hi + 1] - rows[lo])
+
+
+def broadcast_nccl_id(lib, rank: int, group=None) -> bytes:
+    """ncclUniqueId created on rank 0 and broadcast through torch.distributed (any backend)."""
+    import torch
+    import torch.distributed as dist
+    buf = (C.c_ubyte * L.NCCL_ID_BYTES)()
+    if rank == 0:
+        L.check(lib.cgb_nccl_unique_id(buf))
+    t = torch.tensor(list(bytes(buf)), dtype=torch.uint8)
+    if dist.get_backend(group) == "nccl":
+        t = t.cuda()
+    dist.broadcast(t, 0, group=group)
+    return bytes(t.cpu().tolist())
+
+
+class DistCG:
+    """CG over a row-partitioned matrix: this rank owns global rows [row_starts[rank], row_starts[rank+1]).
+    Halo entries of p travel over NVLink, the two scalars per iteration are all-reduced (cgb_dist_*)."""
+
+    def __init__(self, ctx: Context, rank: int, world: int, nccl_id: bytes, row_starts, A_local: Matrix, **opts):
+        self.ctx, self.rank, self.world = ctx, rank, world
+        self.row_starts = np.ascontiguousarray(row_starts, dtype=np.int64)
+        self.A = A_local
+        self.opts = opts
+        self.stats = None
+        h = C.c_void_p()
+        L.check(ctx.lib.cgb_dist_create(ctx.h, rank, world, nccl_id, _p(self.row_starts), A_local.h, C.byref(h)))
+        self.h = h
+        self.n_local = int(self.row_starts[rank + 1] - self.row_starts[rank])
+
+    def set_matrix(self, row_starts, A_local: Matrix):
+        self.row_starts = np.ascontiguousarray(row_starts, dtype=np.int64)
+        self.A = A_local
+        L.check(self.ctx.lib.cgb_dist_set_matrix(self.h, _p(self.row_starts), A_local.h))
+
+    def halo_count(self) -> int:
+        return int(self.ctx.lib.cgb_dist_halo_count(self.h))
+
+    def solve(self, b: Vector, x: Vector, tol: float, max_iter: int = -1):
+        o = make_opts(**self.opts)
+        st = L.CgStats()
+        L.check(self.ctx.lib.cgb_dist_cg_solve(self.h, b.ptr, x.ptr, float(tol), int(max_iter), C.byref(o), C.byref(st)))
+        self.stats = st.as_dict()
+        return self.stats
+
+    def residual(self, x: Vector, b: Vector):
+        rr, xx = C.c_double(), C.c_double()
+        L.check(self.ctx.lib.cgb_dist_residual(self.h, x.ptr, b.ptr, C.byref(rr), C.byref(xx)))
+        return rr.value, xx.value
+
+    def close(self):
+        if self.h:
+            self.ctx.lib.cgb_dist_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,22 @@
+"""Row-partitioned multi-GPU CG vs the single-process oracle (needs >= 2 B200; skipped otherwise)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conjugategradient_b200 import _lib as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dist_solve_matches_oracle(world):
+    if L.load().cgb_device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29610 + world), os.path.join(ROOT, "tests", "dist_worker.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
+    assert out.stdout.count("DIST_OK") == 4 and "DIST_FAIL" not in out.stdout, out.stdout

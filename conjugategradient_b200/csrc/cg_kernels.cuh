@@ -149,13 +149,9 @@ __global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restri
 // the state.  Multi-GPU: alpha = rr / *pAp_in (the all-reduced p.Ap) is also stored to the state for
 // the deferred x update, the local r.r partial goes to *local_out and cg_advance_kernel advances the
 // state after the second all-reduce.
-static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__restrict__ r,
-                                                            const double *__restrict__ Ap, CgState *st,
-                                                            double *partials, double *hist, const double *pAp_in,
-                                                            double *local_out) {
-  if (!cg_active(st)) return;
-  __shared__ double red[32];
-  const double alpha = pAp_in ? st->rr / *pAp_in : st->alpha;
+// r -= alpha Ap over a grid-stride range; returns this thread's share of r.r
+__device__ __forceinline__ double cg_update_body(int64_t n, double *__restrict__ r, const double *__restrict__ Ap,
+                                                 double alpha) {
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   const int64_t n2 = n >> 1;
   double2 *r2 = reinterpret_cast<double2 *>(r);
@@ -175,23 +171,39 @@ static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, dou
     r[n - 1] = rv;
     acc = fma(rv, rv, acc);
   }
+  return acc;
+}
+
+// End of a trip (one thread): stop test on the rr from BEFORE this trip's update (src/CG.hpp:396-404),
+// beta = rr'/rr (:414), rr = rr' (:415), ++trip counter.
+__device__ __forceinline__ void cg_advance_state(CgState *st, double rr_new, double *hist) {
+  const double rr = st->rr;
+  if (isnan(rr) || sqrt(rr) <= st->tol) {
+    st->done = 1;
+    if (isnan(rr)) st->nan_stop = 1;
+  }
+  st->beta = rr_new / rr;
+  st->rr = rr_new;
+  const long long it = st->iter + 1;
+  st->iter = it;
+  if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
+}
+
+static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, double *__restrict__ r,
+                                                            const double *__restrict__ Ap, CgState *st,
+                                                            double *partials, double *hist, const double *pAp_in,
+                                                            double *local_out) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  const double alpha = pAp_in ? st->rr / *pAp_in : st->alpha;
+  double acc = cg_update_body(n, r, Ap, alpha);
   acc = block_sum(acc, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = acc;
   if (publish_and_elect(&st->ticket, gridDim.x)) {
     const double rr_new = reduce_partials(partials, gridDim.x, red);
     if (threadIdx.x == 0) {
       if (!local_out) {
-        const double rr = st->rr;
-        // stop test reads the rr from BEFORE this iteration's update (src/CG.hpp:396-404)
-        if (isnan(rr) || sqrt(rr) <= st->tol) {
-          st->done = 1;
-          if (isnan(rr)) st->nan_stop = 1;
-        }
-        st->beta = rr_new / rr; // :414
-        st->rr = rr_new;        // :415
-        const long long it = st->iter + 1;
-        st->iter = it;
-        if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
+        cg_advance_state(st, rr_new, hist);
       } else {
         st->alpha = alpha; // every CTA used this value; kept for the deferred x update
         *local_out = rr_new;
@@ -223,20 +235,11 @@ static __global__ void __launch_bounds__(kBlock) cg_xflush_kernel(int64_t n, dou
   if ((n & 1) && tid == 0) x[n - 1] = fma(alpha, p[n - 1], x[n - 1]);
 }
 
-// Multi-GPU: advance the state from the all-reduced scalars (one thread).
+// Multi-GPU (NCCL transport): advance the state from the all-reduced scalars (one thread).
 static __global__ void cg_advance_kernel(CgState *st, const double *rr_global, double *hist) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   if (!cg_active(st)) return;
-  const double rr = st->rr, rr_new = *rr_global;
-  if (isnan(rr) || sqrt(rr) <= st->tol) {
-    st->done = 1;
-    if (isnan(rr)) st->nan_stop = 1;
-  }
-  st->beta = rr_new / rr;
-  st->rr = rr_new;
-  const long long it = st->iter + 1;
-  st->iter = it;
-  if (st->record_history && it < st->hist_cap) hist[it] = rr_new;
+  cg_advance_state(st, *rr_global, hist);
 }
 
 // ---- K4 -------------------------------------------------------------------------------------

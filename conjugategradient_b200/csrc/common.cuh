@@ -55,6 +55,8 @@ struct CgState {
   unsigned int ticket; // last-block counter, always returned to 0 by the last block
   int record_history;
   long long hist_cap;
+  int comm_error; // multi-GPU: a peer wait timed out (the loop is stopped, the host reports it)
+  int pad_;
 };
 
 struct Workspace;

@@ -4,10 +4,17 @@
 // is split once, on the device, into
 //   A_loc  : all local rows, only the columns it owns (indices rebased to the block), and
 //   A_halo : only the rows that touch remote columns, indices into a compact halo buffer.
-// Per iteration:  p-update -> pack boundary entries of p -> NCCL send/recv on a side stream,
-// overlapped with the A_loc SpMV -> A_halo correction -> all-reduce p.Ap -> x/r update ->
-// all-reduce r.r -> state advance.  NCCL is resolved with dlopen so single-GPU users never need it.
+// Per iteration (peer transport, the default; peer.cuh): p-update -> pack kernel stores the boundary
+// entries of p into the owners' halo buffers over NVLink and raises their flags -> A_loc SpMV (the
+// transfer overlaps it) -> halo kernel waits for its flags, adds the A_halo correction to Ap and
+// p.Ap and all-reduces p.Ap in its last CTA -> r update + r.r, all-reduced in the last CTA, which
+// also advances the state.  Five launches, no library collective in the loop.
+// NCCL transport (fallback when cudaIpc peer mapping is unavailable, CGB_DIST_TRANSPORT=nccl, and
+// the comparison point): ncclSend/Recv on a side stream + two ncclAllReduce + a state kernel.
+// NCCL is resolved with dlopen so single-GPU users never need it; it always carries the set-up
+// exchanges (receive lists, IPC handles).
 #include "launch.cuh"
+#include "peer.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -68,6 +75,16 @@ int nccl_load() {
   } while (0)
 } // namespace
 
+namespace cgb {
+struct PeerSend { // where the entries of the packed send list go: slice q -> dst[q][0 .. soff[q+1]-soff[q])
+  long long soff[kMaxRanks + 1];
+  double *dst[kMaxRanks];
+};
+struct PeerRecv {
+  int from[kMaxRanks]; // 1 where this rank receives halo entries from that rank
+};
+} // namespace cgb
+
 struct cgb_dist {
   cgb_ctx *ctx = nullptr;
   int rank = 0, nranks = 1;
@@ -87,6 +104,17 @@ struct cgb_dist {
   double *scal = nullptr;      // [0] pAp local, [1] pAp global, [2] rr local, [3] rr global, [4..5] residual
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_pack = nullptr, ev_halo = nullptr;
+  // peer transport (peer.cuh)
+  bool peer = false;
+  size_t halo_bytes = 0;                // size of the halo allocation (IPC-exported)
+  PeerWin *win = nullptr;               // this rank's window
+  std::vector<PeerWin *> win_of;        // all ranks' windows as mapped here (win_of[rank] == win)
+  PeerWin **d_win = nullptr;            // the same, on the device
+  PeerSeq *seq = nullptr;
+  std::vector<double *> halo_of;        // peers' halo buffers as mapped here (nullptr where nothing is sent)
+  PeerSend send;                        // destination table of the pack kernel
+  PeerRecv recv;                        // which ranks this rank receives from
+  PeerCtx pctx() const { return PeerCtx{rank, nranks, d_win, seq}; }
 };
 
 namespace {
@@ -277,6 +305,172 @@ __global__ void __launch_bounds__(kBlock) dist_resid_kernel(int64_t n, const dou
   }
 }
 
+// ---- peer transport kernels (peer.cuh) ---------------------------------------------------------------
+__device__ __forceinline__ void peer_fail(CgState *st) { // a wait timed out: stop the loop, tell the host
+  st->comm_error = 1;
+  st->done = 1;
+}
+
+// Boundary entries of `vec` go straight into the owners' halo buffers (NVLink stores); the last CTA
+// raises this rank's flag in every destination window.
+__global__ void __launch_bounds__(kBlock) peer_pack_kernel(int64_t S, const int *__restrict__ send_idx,
+                                                            const double *__restrict__ vec, PeerSend ps, PeerCtx pc,
+                                                            CgState *st, int gated) {
+  if (gated && !cg_active(st)) return;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t k = tid; k < S; k += nthr) {
+    int q = 0;
+    while (k >= ps.soff[q + 1]) q++;
+    ps.dst[q][k - ps.soff[q]] = vec[send_idx[k]];
+  }
+  __threadfence_system();
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const unsigned long long s = pc.seq->halo + 1;
+    const int q = threadIdx.x;
+    if (q < pc.nranks && ps.soff[q + 1] > ps.soff[q]) {
+      __threadfence_system();
+      st_release_sys_u64(&pc.win[q]->hflag[pc.rank], s);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) pc.seq->halo = s;
+  }
+}
+
+// y[halo_rows[k]] += A_halo[k,:] . halo after the halos have arrived.
+// MODE 1 (CG loop): also p.Ap = base + correction, all-reduced over the ranks, alpha = rr / p.Ap.
+// MODE 0 (set-up, residual): correction only.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) peer_halo_kernel(int64_t nh, const int *__restrict__ rowptr,
+                                                            const int *__restrict__ cols,
+                                                            const double *__restrict__ vals,
+                                                            const int *__restrict__ halo_rows, const double *halo,
+                                                            double *y, const double *p, const double *base, PeerCtx pc,
+                                                            PeerRecv pr, CgState *st, int gated, double *partials) {
+  if (gated && !cg_active(st)) return;
+  __shared__ double red[32];
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if (threadIdx.x < pc.nranks && pr.from[threadIdx.x]) {
+    if (!peer_wait(&pc.win[pc.rank]->hflag[threadIdx.x], pc.seq->halo)) s_ok = 0;
+  }
+  __syncthreads();
+  const bool ok_wait = s_ok != 0;
+  double acc = 0.0;
+  if (ok_wait) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = tid; k < nh; k += nthr) {
+      double s = 0.0;
+      for (int j = rowptr[k]; j < rowptr[k + 1]; j++) s = fma(vals[j], __ldcg(halo + cols[j]), s);
+      const int row = halo_rows[k];
+      y[row] += s;
+      if (MODE == 1) acc = fma(p[row], s, acc);
+    }
+  } else if (threadIdx.x == 0) {
+    peer_fail(st);
+  }
+  if (MODE == 1) {
+    acc = block_sum(acc, red);
+    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+    if (publish_and_elect(&st->ticket, gridDim.x)) {
+      const double corr = reduce_partials(partials, gridDim.x, red);
+      bool ok = true;
+      const double pAp = peer_allreduce(pc, base[0] + corr, &ok);
+      if (threadIdx.x == 0) {
+        if (!ok) peer_fail(st);
+        st->pAp = pAp;
+        st->alpha = st->rr / pAp; // src/CG.hpp:385-386
+      }
+    }
+  }
+}
+
+// K2 with the r.r all-reduce and the state advance in the last CTA.
+__global__ void __launch_bounds__(kBlock) peer_update_kernel(int64_t n, double *__restrict__ r,
+                                                              const double *__restrict__ Ap, CgState *st,
+                                                              double *partials, double *hist, PeerCtx pc) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  double acc = cg_update_body(n, r, Ap, st->alpha);
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double local = reduce_partials(partials, gridDim.x, red);
+    bool ok = true;
+    const double rr_new = peer_allreduce(pc, local, &ok);
+    if (threadIdx.x == 0) {
+      if (!ok) peer_fail(st);
+      else cg_advance_state(st, rr_new, hist);
+    }
+  }
+}
+
+// r = b - t, rr = all-reduce(r.r), arm the state          (dist flavour of K0, src/CG.hpp:324-341)
+__global__ void __launch_bounds__(kBlock) peer_init_kernel(int64_t n, const double *__restrict__ b,
+                                                            const double *__restrict__ t, double *__restrict__ r,
+                                                            CgState *st, double *partials, double *hist, PeerCtx pc) {
+  __shared__ double red[32];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double acc = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double ri = b[i] - t[i];
+    r[i] = ri;
+    acc = fma(ri, ri, acc);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double local = reduce_partials(partials, gridDim.x, red);
+    bool ok = true;
+    const double rr = peer_allreduce(pc, local, &ok);
+    if (threadIdx.x == 0) {
+      st->rr = rr;
+      st->rr0 = rr;
+      st->pAp = 0.0;
+      st->alpha = 0.0;
+      st->beta = 0.0;
+      st->iter = 0;
+      st->nan_stop = 0;
+      if (st->record_history && st->hist_cap > 0) hist[0] = rr;
+      if (ok) st->done = 0;
+      else st->comm_error = 1; // stays disarmed
+    }
+  }
+}
+
+// sum (b - t)^2 and sum x^2, all-reduced -> out[0], out[1]; out[2] = 1 on a peer timeout
+__global__ void __launch_bounds__(kBlock) peer_resid_kernel(int64_t n, const double *__restrict__ b,
+                                                             const double *__restrict__ t,
+                                                             const double *__restrict__ x, CgState *st,
+                                                             double *partials, double *out, PeerCtx pc) {
+  __shared__ double red[32];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double a0 = 0.0, a1 = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double a = b[i] - t[i];
+    a0 = fma(a, a, a0);
+    a1 = fma(x[i], x[i], a1);
+  }
+  a0 = block_sum(a0, red);
+  a1 = block_sum(a1, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = a0;
+    partials[kMaxPartials + blockIdx.x] = a1;
+  }
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double s0 = reduce_partials(partials, gridDim.x, red);
+    const double s1 = reduce_partials(partials + kMaxPartials, gridDim.x, red);
+    bool ok = true;
+    const double g0 = peer_allreduce(pc, s0, &ok);
+    const double g1 = peer_allreduce(pc, s1, &ok);
+    if (threadIdx.x == 0) {
+      out[0] = g0;
+      out[1] = g1;
+      out[2] = ok ? 0.0 : 1.0;
+    }
+  }
+}
+
 template <class T>
 int d2h_vec(cgb_ctx *ctx, std::vector<T> &out, const T *d, size_t n) {
   out.resize(n);
@@ -293,6 +487,12 @@ int owner_of(const std::vector<int64_t> &rs, int64_t col) {
 // On return the comm stream has ev_halo recorded; the caller makes the main stream wait for it.
 int halo_exchange(cgb_dist *d, const double *vec, int gated) {
   cudaStream_t s = d->ctx->stream, c = d->comm_stream;
+  if (d->peer) {
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->S + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 2));
+    peer_pack_kernel<<<grid, kBlock, 0, s>>>(d->S, d->send_idx, vec, d->send, d->pctx(), d->Aloc->ws.st, gated);
+    CGB_CUDA(cudaGetLastError());
+    return CGB_OK;
+  }
   if (d->S > 0) {
     const int grid = (int)std::min<int64_t>((d->S + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 2);
     pack_kernel<<<grid, kBlock, 0, s>>>(d->S, d->send_idx, vec, d->send_buf, d->Aloc->ws.st, gated);
@@ -310,7 +510,24 @@ int halo_exchange(cgb_dist *d, const double *vec, int gated) {
   return CGB_OK;
 }
 
+// peer transport: wait for the halos, add the A_halo part; mode 1 also all-reduces p.Ap and forms alpha
+int peer_halo_apply(cgb_dist *d, double *y, const double *p, const double *base, int mode, int gated) {
+  cudaStream_t s = d->ctx->stream;
+  Workspace &w = d->Aloc->ws;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->nh + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 4));
+  const cgb_csr *H = d->Ahalo;
+  if (mode == 1)
+    peer_halo_kernel<1><<<grid, kBlock, 0, s>>>(d->nh, H->rowptr, H->cols, H->vals, d->halo_rows, d->halo, y, p, base,
+                                                d->pctx(), d->recv, w.st, gated, w.partials);
+  else
+    peer_halo_kernel<0><<<grid, kBlock, 0, s>>>(d->nh, H->rowptr, H->cols, H->vals, d->halo_rows, d->halo, y, p, base,
+                                                d->pctx(), d->recv, w.st, gated, w.partials);
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
 int halo_apply(cgb_dist *d, double *y, const double *p, const double *base, double *out, int gated) {
+  if (d->peer) return peer_halo_apply(d, y, p, base, 0, gated);
   cudaStream_t s = d->ctx->stream;
   CGB_CUDA(cudaStreamWaitEvent(s, d->ev_halo, 0));
   Workspace &w = d->Aloc->ws;
@@ -368,9 +585,21 @@ int cgb_plan_halo(int rank, int nranks, const int64_t *row_starts, int64_t nnz_l
   return CGB_OK;
 }
 
+// every rank has unmapped the others' halo buffers before anyone frees its own (collective)
+static void peer_release_halo(cgb_dist *d) {
+  for (size_t q = 0; q < d->halo_of.size(); q++)
+    if ((int)q != d->rank && d->halo_of[q]) cudaIpcCloseMemHandle(d->halo_of[q]);
+  d->halo_of.clear();
+  if (d->peer && d->comm && d->scal) { // barrier
+    g_nccl.AllReduce(d->scal + 6, d->scal + 7, 1, ncclDouble, ncclSum, d->comm, d->ctx->stream);
+    cudaStreamSynchronize(d->ctx->stream);
+  }
+}
+
 static void dist_release_matrix(cgb_dist *d) {
   cudaStreamSynchronize(d->ctx->stream);
   if (d->comm_stream) cudaStreamSynchronize(d->comm_stream);
+  if (d->Aloc) peer_release_halo(d);
   cgb_csr_destroy(d->Aloc);
   cgb_csr_destroy(d->Ahalo);
   cudaFree(d->halo_rows);
@@ -389,6 +618,15 @@ int cgb_dist_destroy(cgb_dist *d) {
   if (!d) return CGB_OK;
   ScopedDevice sd(d->ctx->device);
   dist_release_matrix(d);
+  for (size_t q = 0; q < d->win_of.size(); q++)
+    if ((int)q != d->rank && d->win_of[q]) cudaIpcCloseMemHandle(d->win_of[q]);
+  if (d->peer && d->comm && d->scal) { // nobody frees its window while a peer still maps it
+    g_nccl.AllReduce(d->scal + 6, d->scal + 7, 1, ncclDouble, ncclSum, d->comm, d->ctx->stream);
+    cudaStreamSynchronize(d->ctx->stream);
+  }
+  cudaFree(d->win);
+  cudaFree(d->d_win);
+  cudaFree(d->seq);
   if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
   cudaFree(d->scal);
   if (d->ev_pack) cudaEventDestroy(d->ev_pack);

@@ -25,6 +25,122 @@ int read_int(cgb_ctx *ctx, const int *d, int *out) {
   return CGB_OK;
 }
 
+
+// ---- peer transport set-up (peer.cuh) -------------------------------------------------------------
+// All-gather of one cudaIpcMemHandle_t per rank (through NCCL; set-up only).
+int gather_ipc_handles(cgb_dist *d, const cudaIpcMemHandle_t &mine, std::vector<cudaIpcMemHandle_t> &all) {
+  const int P = d->nranks;
+  cudaStream_t s = d->ctx->stream;
+  DevBuf b_in, b_out;
+  CGB_TRY(dev_alloc(b_in, sizeof(cudaIpcMemHandle_t)));
+  CGB_TRY(dev_alloc(b_out, sizeof(cudaIpcMemHandle_t) * (size_t)P));
+  CGB_CUDA(cudaMemcpyAsync(b_in.p, &mine, sizeof(mine), cudaMemcpyHostToDevice, s));
+  CGB_NCCL(g_nccl.AllGather(b_in.p, b_out.p, sizeof(cudaIpcMemHandle_t), ncclChar, d->comm, s));
+  all.resize(P);
+  CGB_CUDA(cudaMemcpyAsync(all.data(), b_out.p, sizeof(cudaIpcMemHandle_t) * (size_t)P, cudaMemcpyDeviceToHost, s));
+  CGB_CUDA(cudaStreamSynchronize(s));
+  return CGB_OK;
+}
+
+// Every rank learns whether ALL ranks succeeded (min over ranks of `ok`).
+int all_agree(cgb_dist *d, int ok, int *all_ok) {
+  cudaStream_t s = d->ctx->stream;
+  const double v = ok ? 1.0 : 0.0;
+  double out = 0.0;
+  CGB_CUDA(cudaMemcpyAsync(d->scal + 6, &v, sizeof(double), cudaMemcpyHostToDevice, s));
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 6, d->scal + 7, 1, ncclDouble, ncclMin, d->comm, s));
+  CGB_CUDA(cudaMemcpyAsync(&out, d->scal + 7, sizeof(double), cudaMemcpyDeviceToHost, s));
+  CGB_CUDA(cudaStreamSynchronize(s));
+  *all_ok = out > 0.5;
+  return CGB_OK;
+}
+
+constexpr size_t kIpcGranule = (size_t)2 << 20; // exported allocations are whole 2 MiB blocks
+
+// Allocate this rank's window, map every peer's window.  Leaves d->peer = true only if it worked everywhere.
+int peer_window_setup(cgb_dist *d) {
+  d->peer = false;
+  const char *env = getenv("CGB_DIST_TRANSPORT");
+  int want = !(env && !strcmp(env, "nccl")) && d->nranks <= kMaxRanks;
+  int ok = want;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (ok) {
+    ok = cudaMalloc(&d->win, kIpcGranule) == cudaSuccess && cudaMemset(d->win, 0, kIpcGranule) == cudaSuccess &&
+         cudaMalloc(&d->seq, sizeof(PeerSeq)) == cudaSuccess && cudaMemset(d->seq, 0, sizeof(PeerSeq)) == cudaSuccess &&
+         cudaMalloc(&d->d_win, sizeof(PeerWin *) * kMaxRanks) == cudaSuccess &&
+         cudaIpcGetMemHandle(&mine, d->win) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+  }
+  std::vector<cudaIpcMemHandle_t> all;
+  CGB_TRY(gather_ipc_handles(d, mine, all)); // collective: every rank takes part, successful or not
+  int everyone = 0;
+  CGB_TRY(all_agree(d, ok, &everyone));
+  d->win_of.assign(d->nranks, nullptr);
+  if (everyone) {
+    d->win_of[d->rank] = d->win;
+    for (int q = 0; q < d->nranks && ok; q++) {
+      if (q == d->rank) continue;
+      void *ptr = nullptr;
+      if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+      } else {
+        d->win_of[q] = (PeerWin *)ptr;
+      }
+    }
+    CGB_TRY(all_agree(d, ok, &everyone));
+  }
+  if (everyone) {
+    CGB_CUDA(cudaMemcpy(d->d_win, d->win_of.data(), sizeof(PeerWin *) * (size_t)d->nranks, cudaMemcpyHostToDevice));
+    d->peer = true;
+  } else {
+    for (int q = 0; q < d->nranks; q++)
+      if (q != d->rank && d->win_of[q]) cudaIpcCloseMemHandle(d->win_of[q]);
+    d->win_of.clear();
+    if (want && d->rank == 0 && getenv("CGB_VERBOSE"))
+      fprintf(stderr, "cgb200: peer-memory transport unavailable, using NCCL send/recv + all-reduce\n");
+  }
+  return CGB_OK;
+}
+
+// After the halo buffer of the current matrix exists: map the peers' halo buffers this rank sends
+// into and build the destination table of the pack kernel.  M = all-gathered receive counts
+// (M[q*P + r] = entries rank q receives from rank r).
+int peer_halo_setup(cgb_dist *d, const std::vector<int64_t> &M) {
+  const int P = d->nranks;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  int ok = cudaIpcGetMemHandle(&mine, d->halo) == cudaSuccess;
+  if (!ok) cudaGetLastError();
+  std::vector<cudaIpcMemHandle_t> all;
+  CGB_TRY(gather_ipc_handles(d, mine, all));
+  d->halo_of.assign(P, nullptr);
+  memset(&d->send, 0, sizeof(d->send));
+  memset(&d->recv, 0, sizeof(d->recv));
+  for (int q = 0; q < P; q++) {
+    d->send.soff[q] = d->soff[q];
+    d->recv.from[q] = d->rcount[q] > 0;
+    if (q == d->rank || d->scount[q] == 0 || !ok) continue;
+    void *ptr = nullptr;
+    if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      ok = 0;
+      continue;
+    }
+    d->halo_of[q] = (double *)ptr;
+    int64_t off = 0; // where this rank's entries start in q's halo buffer: q receives from ranks in rank order
+    for (int r = 0; r < d->rank; r++) off += M[(size_t)q * P + r];
+    d->send.dst[q] = d->halo_of[q] + off;
+  }
+  d->send.soff[P] = d->soff[P];
+  for (int q = P + 1; q <= kMaxRanks; q++) d->send.soff[q] = d->soff[P];
+  int everyone = 0;
+  CGB_TRY(all_agree(d, ok, &everyone));
+  if (!everyone) return fail(CGB_ERR_NCCL, "peer transport: mapping a peer's halo buffer failed (set CGB_DIST_TRANSPORT=nccl)");
+  return CGB_OK;
+}
+
 int dist_setup(cgb_dist *d, cgb_csr *A) {
   cgb_ctx *ctx = d->ctx;
   cudaStream_t s = ctx->stream;
@@ -153,8 +269,9 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   d->S = d->soff[P];
   CGB_CUDA(cudaMalloc(&d->send_idx, sizeof(int32_t) * (size_t)(d->S + 1)));
   CGB_CUDA(cudaMalloc(&d->send_buf, sizeof(double) * (size_t)(d->S + 1)));
-  CGB_CUDA(cudaMalloc(&d->halo, sizeof(double) * (size_t)(H + 1)));
-  CGB_CUDA(cudaMemsetAsync(d->halo, 0, sizeof(double) * (size_t)(H + 1), s));
+  d->halo_bytes = ((sizeof(double) * (size_t)(H + 1) + kIpcGranule - 1) / kIpcGranule) * kIpcGranule;
+  CGB_CUDA(cudaMalloc(&d->halo, d->halo_bytes));
+  CGB_CUDA(cudaMemsetAsync(d->halo, 0, d->halo_bytes, s));
   CGB_NCCL(g_nccl.GroupStart());
   for (int q = 0; q < P; q++) {
     if (d->rcount[q] > 0) CGB_NCCL(g_nccl.Send(recv_cols + d->roff[q], (size_t)d->rcount[q], ncclInt32, q, d->comm, s));
@@ -166,6 +283,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
     CGB_CUDA(cudaGetLastError());
   }
   CGB_CUDA(cudaStreamSynchronize(s));
+  if (d->peer) CGB_TRY(peer_halo_setup(d, M));
   return CGB_OK;
 }
 
@@ -185,6 +303,12 @@ int dist_enqueue_iteration(cgb_dist *d, double *x) {
     launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
                   w.p1, w.Ap, x, w.st, w.partials, d->scal + 0);
   });
+  if (d->peer) { // halo correction + all-reduce(p.Ap) + alpha, then r update + all-reduce(r.r) + state advance
+    CGB_TRY(peer_halo_apply(d, w.Ap, w.p0, d->scal + 0, 1, 1));
+    peer_update_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, d->pctx());
+    CGB_CUDA(cudaGetLastError());
+    return CGB_OK;
+  }
   CGB_TRY(halo_apply(d, w.Ap, w.p0, d->scal + 0, d->scal + 0, 1));
   CGB_NCCL(g_nccl.AllReduce(d->scal + 0, d->scal + 1, 1, ncclDouble, ncclSum, d->comm, s));
   cg_update_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, d->scal + 1, d->scal + 2);
@@ -226,16 +350,18 @@ int cgb_dist_create(cgb_ctx *ctx, int rank, int nranks, const void *h_id128, con
     cudaError_t e = cudaStreamCreateWithFlags(&d->comm_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_pack, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_halo, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaMalloc(&d->scal, sizeof(double) * 8);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d->scal, 0, sizeof(double) * 8, ctx->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&d->scal, sizeof(double) * 16);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->scal, 0, sizeof(double) * 16, ctx->stream);
     if (e != cudaSuccess) {
       rc = fail(CGB_ERR_CUDA, "cgb_dist_create: %s", cudaGetErrorString(e));
       break;
     }
-    rc = dist_setup(d, A);
+    rc = peer_window_setup(d);
+    if (rc == CGB_OK) rc = dist_setup(d, A);
   } while (0);
   if (rc != CGB_OK) {
     std::string keep = cgb_last_error();
+    d->peer = false; // no collective barriers while tearing down a half-built handle
     cgb_dist_destroy(d);
     set_error("%s", keep.c_str());
     return rc;
@@ -299,14 +425,20 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   CGB_TRY(halo_exchange(d, d_x, 0));
   if (n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
   CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
-  dist_init_kernel<<<A->grid_vec, kBlock, 0, s>>>(n, d_b, w.Ap, w.r, w.st, w.partials, d->scal + 2);
-  CGB_CUDA(cudaGetLastError());
-  CGB_NCCL(g_nccl.AllReduce(d->scal + 2, d->scal + 3, 1, ncclDouble, ncclSum, d->comm, s));
-  dist_arm_kernel<<<1, 32, 0, s>>>(w.st, d->scal + 3, w.hist);
+  if (d->peer) {
+    peer_init_kernel<<<A->grid_vec, kBlock, 0, s>>>(n, d_b, w.Ap, w.r, w.st, w.partials, w.hist, d->pctx());
+  } else {
+    dist_init_kernel<<<A->grid_vec, kBlock, 0, s>>>(n, d_b, w.Ap, w.r, w.st, w.partials, d->scal + 2);
+    CGB_CUDA(cudaGetLastError());
+    CGB_NCCL(g_nccl.AllReduce(d->scal + 2, d->scal + 3, 1, ncclDouble, ncclSum, d->comm, s));
+    dist_arm_kernel<<<1, 32, 0, s>>>(w.st, d->scal + 3, w.hist);
+  }
   CGB_CUDA(cudaGetLastError());
 
-  int64_t launches = 6;
-  if (use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != (uint64_t)batch)) {
+  const int per_iter = d->peer ? 5 : 6; // kernels of ours per iteration (NCCL's own kernels not counted)
+  int64_t launches = d->peer ? 4 : 5;
+  const uint64_t gkey = ((uint64_t)batch << 1) | (d->peer ? 1u : 0u);
+  if (use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != gkey)) {
     if (w.graph) {
       cudaGraphExecDestroy(w.graph);
       w.graph = nullptr;
@@ -327,7 +459,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
       w.graph = nullptr;
       return fail(CGB_ERR_CUDA, "cudaGraphInstantiate (dist): %s", cudaGetErrorString(e));
     }
-    w.graph_key = (uint64_t)batch;
+    w.graph_key = gkey;
     w.graph_x = d_x;
   }
   // every rank takes the same decisions: the polled state is built from all-reduced scalars only
@@ -337,11 +469,14 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     } else {
       for (int i = 0; i < batch; i++) CGB_TRY(dist_enqueue_iteration(d, d_x));
     }
-    launches += (int64_t)batch * 6;
+    launches += (int64_t)batch * per_iter;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaStreamSynchronize(s));
-    if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter) break;
+    if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter || w.h_st[0].comm_error) break;
   }
+  if (w.h_st[0].comm_error)
+    return fail(CGB_ERR_NCCL, "cgb_dist_cg_solve: a peer did not answer within the time limit (rank %d, trip %lld)", d->rank,
+                (long long)w.h_st[0].iter);
   if (n > 0) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st); // last trip's x update
   CGB_CUDA(cudaGetLastError());
   launches += 1;
@@ -376,13 +511,21 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
   CGB_TRY(halo_exchange(d, d_x, 0));
   if (A->n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
   CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
-  dist_resid_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, d_b, w.Ap, d_x, w.st, w.partials, d->scal + 4);
-  CGB_CUDA(cudaGetLastError());
-  CGB_NCCL(g_nccl.AllReduce(d->scal + 4, d->scal + 4, 2, ncclDouble, ncclSum, d->comm, s));
-  CGB_CUDA(cudaMemcpyAsync(ctx->pinned, d->scal + 4, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (d->peer) {
+    peer_resid_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, d_b, w.Ap, d_x, w.st, w.partials, d->scal + 8, d->pctx());
+    CGB_CUDA(cudaGetLastError());
+    CGB_CUDA(cudaMemcpyAsync(ctx->pinned, d->scal + 8, 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  } else {
+    dist_resid_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, d_b, w.Ap, d_x, w.st, w.partials, d->scal + 4);
+    CGB_CUDA(cudaGetLastError());
+    CGB_NCCL(g_nccl.AllReduce(d->scal + 4, d->scal + 4, 2, ncclDouble, ncclSum, d->comm, s));
+    CGB_CUDA(cudaMemsetAsync(d->scal + 6, 0, sizeof(double), s));
+    CGB_CUDA(cudaMemcpyAsync(ctx->pinned, d->scal + 4, 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  }
   CGB_CUDA(cudaStreamSynchronize(s));
   *rr = ctx->pinned[0];
   *xx = ctx->pinned[1];
+  if (ctx->pinned[2] != 0.0) return fail(CGB_ERR_NCCL, "cgb_dist_residual: a peer did not answer within the time limit");
   return CGB_OK;
 }
 

@@ -57,11 +57,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(smem_dst)),
-               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
+// The matrix stream is read exactly once per pass: evict-first in L2, so that it does not push the
+// vectors (which are re-read by the next kernel, and gathered several times by this one) out.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar,
+                                            uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
 }
 
 // Row sums of `len` staged entries for one lane of an L-lane group; 4 gathers in flight.
@@ -119,6 +128,7 @@ __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int 
   if (tid >= kTmaConsumers) {
     // ---------------- producer warp: one lane drives the TMA ----------------
     if (tid == kTmaConsumers) {
+      const uint64_t pol = l2_policy_evict_first();
       int stage = 0;
       uint32_t phase = 0;
       // tile bounds are fetched one tile ahead so their latency never sits between two copies
@@ -155,10 +165,10 @@ __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int 
             meta[stage].fallback = 0;
             mbar_expect_tx(&full[stage], bytes);
             if (cnt) {
-              tma_load_1d(sv, vals + j0a, cnt * 8u, &full[stage]);
-              tma_load_1d(sc, cols + j0a, cnt * 4u, &full[stage]);
+              tma_load_1d(sv, vals + j0a, cnt * 8u, &full[stage], pol);
+              tma_load_1d(sc, cols + j0a, cnt * 4u, &full[stage], pol);
             }
-            tma_load_1d(sr, rowptr + r0, (uint32_t)(TILE_ROWS + 4) * 4u, &full[stage]);
+            tma_load_1d(sr, rowptr + r0, (uint32_t)(TILE_ROWS + 4) * 4u, &full[stage], pol);
           }
         }
         if (fb) {

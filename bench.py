@@ -34,6 +34,7 @@ WORKLOADS = {
     "poisson3d_7pt_128": ("3d7", 128, 1e-8),   # C2
     "stencil3d_27pt_256": ("3d27", 256, 1e-8), # C3
     "poisson2d_5pt_128": ("2d5", 128, 1e-8),   # C1
+    "random_spd_10m": ("rspd", 10_000_000, 1e-8),  # C5: power-law row lengths (SELL-32-sigma engine)
 }
 
 
@@ -44,6 +45,8 @@ def b_iter(n, nnz):
 
 def stencil_dims(kind, m):
     from conjugategradient_b200 import generators as G
+    if kind == "rspd":
+        return m, None  # nnz is generator-defined: taken from the generated matrix
     n = m * m if kind == "2d5" else m ** 3
     return n, G.stencil_nnz(kind, m)
 
@@ -118,8 +121,8 @@ def run_reference(args, kind, m, rel):
     cfg_m = m
     n, nnz = stencil_dims(kind, cfg_m)
     t0 = time.time()
-    gen = {"3d7": G.poisson3d_7pt, "3d27": G.stencil3d_27pt, "2d5": G.poisson2d_5pt}[kind]
     vals, cols, rows = gen_host_csr(kind, cfg_m)
+    nnz = int(vals.size)
     b = G.default_rhs(n)
     kind_ref = "reference" if oracle.have_ref("omp") else "port"
     out = time_cpu(vals, cols, rows, b, target_seconds=args.cpu_seconds, steps=args.steps, warmup=args.warmup)
@@ -138,6 +141,9 @@ def run_reference(args, kind, m, rel):
 
 def gen_host_csr(kind, m):
     """Host CSR of the stencil, built directly (no lexsort) so 512^3 takes seconds, not minutes."""
+    if kind == "rspd":  # NumPy twin of the device generator's distribution (same parameters, different RNG stream)
+        from conjugategradient_b200 import generators as G
+        return G.random_spd_powerlaw(m)
     n = m * m if kind == "2d5" else m ** 3
     if kind == "3d27" or m < 64:
         from conjugategradient_b200 import generators as G
@@ -213,7 +219,8 @@ def time_cpu(vals, cols, rows, b, target_seconds, steps, warmup):
 
 
 def config_dict(workload, kind, m, n, nnz, rel, where, **extra):
-    d = {"workload": workload, "matrix": f"{kind} stencil m={m}", "n": n, "nnz": nnz, "format": "CSR fp64/int32",
+    d = {"workload": workload, "matrix": f"{kind} stencil m={m}" if kind != "rspd" else
+         f"random SPD, power-law row lengths (gamma 2.2, d_min 2, d_max 4096), n={m}", "n": n, "nnz": nnz, "format": "CSR fp64/int32",
          "rhs": "b[i]=i+1, x0=0", "tolerance": f"absolute {rel:g}*||b||2 on the recurrence residual (reference stop rule)",
          "step": "one full CG solve", "l2_policy": "inputs larger than L2 (CSR %.1f GB, vectors %.2f GB each)" %
          ((12 * nnz + 4 * n) / 1e9, 8 * n / 1e9), "B_iter_bytes": b_iter(n, nnz), "where": where}
@@ -241,14 +248,17 @@ def run_ours(args, kind, m, rel):
     ctx = S.Context(local_rank)
     lib = ctx.lib
     n, nnz = stencil_dims(kind, m)
-    mz = 1 if kind == "2d5" else m
-    plane = m if kind == "2d5" else m * m
-    planes = m
-    # contiguous slabs of grid planes per rank
-    row_starts = np.array([plane * ((planes * r) // world) for r in range(world + 1)], dtype=np.int64)
+    if kind == "rspd":
+        row_starts = S.partition_rows(n, world)
+    else:
+        plane = m if kind == "2d5" else m * m
+        row_starts = S.partition_rows(n, world, align=plane)  # contiguous slabs of grid planes per rank
     lo, hi = int(row_starts[rank]), int(row_starts[rank + 1])
     nloc = hi - lo
-    A = S.Matrix.stencil(ctx, kind, m, 0 if kind == "2d5" else m, lo, hi)
+    if kind == "rspd":
+        A = S.Matrix.random_spd(ctx, n, row_begin=lo, row_end=hi)
+    else:
+        A = S.Matrix.stencil(ctx, kind, m, 0 if kind == "2d5" else m, lo, hi)
     b_host = np.arange(lo + 1, hi + 1, dtype=np.float64)
     nb = float(np.sqrt(n * (n + 1) * (2 * n + 1) / 6.0))  # ||1..n||_2 in closed form
     tol = rel * nb
@@ -314,6 +324,9 @@ def run_ours(args, kind, m, rel):
         lib.cgb_event_destroy(e1)
         return max_over_ranks(ms.value), outs
 
+    if nnz is None:
+        nnz = int(sum_over_ranks(float(A.NNZ())))
+
     # ---- device-resident solves -----------------------------------------------------------------
     for _ in range(args.warmup):
         solve_resident()
@@ -342,7 +355,8 @@ def run_ours(args, kind, m, rel):
         k1_bytes = 12 * nnz + 4 * (n + 1) + 16 * n  # vals + cols + rowptr + p read + Ap write
         k1_ms = float(np.mean(spmv))
         ach = k1_bytes / (k1_ms * 1e6)
-        roof = {"bound": "hbm", "kernel": "cg_spmv_kernel (CSR SpMV + p.Ap, TMA-staged)", "achieved": ach, "peak": peak,
+        eng = "SELL-32-sigma copy, warp per slice" if last["format"] == L.FMT_SELL else "CSR, TMA-staged tiles"
+        roof = {"bound": "hbm", "kernel": f"cg_spmv_kernel (SpMV + p.Ap; {eng})", "achieved": ach, "peak": peak,
                 "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "traffic": ncu_traffic(args.workload),
                 "bytes_per_launch": k1_bytes, "ms_per_launch": k1_ms,
                 "share_of_iteration": k1_ms / (ms_total / max(iters, 1)),
@@ -401,20 +415,22 @@ def run_ours(args, kind, m, rel):
                "d2h_bytes_per_step": int(d2h), "steps": e_steps, "ms_per_step": e_ms / e_steps,
                "api": "cgb_cg_solve_host (pinned host CSR + b in, x out)" if dh is None else
                       "cgb_csr_create + cgb_dist_set_matrix + cgb_dist_cg_solve + D2H per rank"}
-        x_host = np.array(px, copy=True)
-        for hnd in (pv_h, pc_h, pr_h, pb_h, px_h):
-            lib.cgb_host_free(hnd)
-        del pv, pc, pr, pb, px
 
     # ---- CPU baseline: the reference's own solver on the host cores (N = 1, rank 0) ----------------
     cpu = None
     if world == 1 and not args.no_cpu:
-        vals, cols, rows = gen_host_csr(kind, m)
+        # the very matrix the GPU solved (downloaded for the e2e leg), else the host generator's
+        vals, cols, rows = (pv, pc, pr) if e2e is not None else gen_host_csr(kind, m)
         b_full = G.default_rhs(n)
         import oracle
         out = time_cpu(vals, cols, rows, b_full, target_seconds=args.cpu_seconds, steps=1, warmup=0)
         cpu = {"value": out["value"], "unit": UNIT, "cores": out["cores"],
                "kind": "reference" if oracle.have_ref("omp") else "port", "sample": out["sample"]}
+        del vals, cols, rows
+    if e2e is not None:
+        for hnd in (pv_h, pc_h, pr_h, pb_h, px_h):
+            lib.cgb_host_free(hnd)
+        del pv, pc, pr, pb, px
 
     if rank == 0:
         line = {
@@ -424,7 +440,9 @@ def run_ours(args, kind, m, rel):
             "config": config_dict(args.workload, kind, m, n, nnz, rel, f"{world}xB200",
                                   parallelism=f"row-partitioned x{world}" if world > 1 else "single GPU",
                                   iterations_per_solve=last["iterations"], true_rel_residual=true_rel,
-                                  loop="CUDA graph batches of %d iterations, device-side stop flag" % args.check_every),
+                                  loop="CUDA graph batches of %d iterations, device-side stop flag" % args.check_every,
+                                  engine="SELL-32-sigma" if last["format"] == L.FMT_SELL else "CSR TMA-staged",
+                                  transport=(os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None)),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "achieved_GBps_B_iter": iters * b_iter(n, nnz) / (ms_total * 1e6),
         }

@@ -11,8 +11,26 @@ using namespace cgb;
 
 namespace cgb {
 
+// L2 persisting access-policy window over the gathered vector p (north_star):
+// the matrix stream is evict-first, vector passes are streaming, the window keeps p's lines resident
+// between the p-update that writes them and the SpMV gathers that read them (several times each).
+static cudaAccessPolicyWindow p_window(cgb_ctx *ctx, const double *p, int64_t n) {
+  cudaAccessPolicyWindow w;
+  memset(&w, 0, sizeof(w));
+  size_t bytes = sizeof(double) * (size_t)n;
+  if (bytes > ctx->l2_window_max) bytes = ctx->l2_window_max;
+  w.base_ptr = (void *)p;
+  w.num_bytes = bytes;
+  const double ratio = bytes ? (double)ctx->l2_persist_set / (double)bytes : 0.0;
+  w.hitRatio = (float)(ratio > 1.0 ? 1.0 : ratio);
+  w.hitProp = cudaAccessPropertyPersisting;
+  w.missProp = cudaAccessPropertyStreaming;
+  return w;
+}
+
 struct LoopCfg {
   bool fused;
+  bool l2_window;
   bool time_kernels;
   SpmvLaunch sl;
   int grid_vec;
@@ -32,7 +50,7 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
   CGB_CUDA(mark(1));
   dispatch_lanes(c.sl.lanes, c.sl.tma, [&](auto Lc, auto Tc) {
     constexpr int L = decltype(Lc)::value;
-    constexpr bool T = decltype(Tc)::value;
+    constexpr int T = decltype(Tc)::value;
     if (c.fused)
       launch_kernel(cg_spmv_kernel<L, T, true>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, x, w.st, w.partials,
                     (double *)nullptr);
@@ -66,6 +84,21 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
     return rc;
   }
   if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+  if (c.l2_window) { // kernel nodes carry the access-policy window themselves
+    size_t nn = 0;
+    cudaGraphGetNodes(g, nullptr, &nn);
+    std::vector<cudaGraphNode_t> nodes(nn);
+    cudaGraphGetNodes(g, nodes.data(), &nn);
+    cudaKernelNodeAttrValue v;
+    memset(&v, 0, sizeof(v));
+    v.accessPolicyWindow = p_window(A->ctx, w.p0, A->n);
+    for (size_t i = 0; i < nn; i++) {
+      cudaGraphNodeType t;
+      if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel)
+        cudaGraphKernelNodeSetAttribute(nodes[i], cudaKernelNodeAttributeAccessPolicyWindow, &v);
+    }
+    cudaGetLastError();
+  }
   e = cudaGraphInstantiate(&w.graph, g, 0);
   cudaGraphDestroy(g);
   if (e != cudaSuccess) {
@@ -111,9 +144,38 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
   const bool fused = o.fuse_p_update != 0;
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
+  CGB_TRY(csr_prepare(A));
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
-  LoopCfg cfg{fused, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup};
+  // L2 window: explicit option, or CGB_L2_WINDOW=1/0; only meaningful without the fused p-update (p ping-pongs there)
+  bool l2w = o.l2_persist_p != 0;
+  if (const char *e = getenv("CGB_L2_WINDOW")) l2w = atoi(e) != 0;
+  l2w = l2w && !fused && ctx->l2_persist_max > 0 && ctx->l2_window_max > 0;
+  if (l2w && ctx->l2_persist_set == 0) {
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_persist_max) == cudaSuccess) ctx->l2_persist_set = ctx->l2_persist_max;
+    else {
+      cudaGetLastError();
+      l2w = false;
+    }
+  }
+  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup};
+  if (l2w) {
+    cudaStreamAttrValue v;
+    memset(&v, 0, sizeof(v));
+    v.accessPolicyWindow = p_window(ctx, w.p0, n);
+    CGB_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v));
+  }
+  struct WindowGuard { // the window never outlives the solve
+    cudaStream_t s;
+    bool on;
+    ~WindowGuard() {
+      if (!on) return;
+      cudaStreamAttrValue v;
+      memset(&v, 0, sizeof(v));
+      cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v);
+      cudaCtxResetPersistingL2Cache();
+    }
+  } wguard{s, l2w};
   if (cfg.time_kernels)
     for (auto &e : w.ev)
       if (!e) CGB_CUDA(cudaEventCreate(&e));
@@ -154,7 +216,8 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   int64_t samples = 0;
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
-                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.tma << 2);
+                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.tma << 2) ^
+                         ((uint64_t)cfg.l2_window << 4);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an
@@ -232,7 +295,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     }
     stats->kernel_launches = launches;
     stats->loop_mode = mode;
-    stats->format = CGB_FMT_CSR;
+    stats->format = cfg.sl.tma == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
   }
   return CGB_OK;
 }

@@ -29,20 +29,34 @@ struct CsrView {
   const int *rowptr;
   const int *cols;
   const double *vals;
+  // SELL-32-sigma shadow copy (engine kEngSell only)
+  int64_t sell_slices;
+  const int64_t *sell_off;
+  const int *sell_cols;
+  const double *sell_vals;
+  const int *sell_perm;
+  int64_t sell_nlong;
+  const int *sell_long;
+  const int64_t *sell_chunk;
+  int sell_warp_chunks;
 };
 
-// One entry point for both row engines: TMA-staged tiles (288 threads, dynamic shared memory) or
-// direct loads with L lanes per row (256 threads).
-template <int L, bool TMA, class G, class E>
+// One entry point for the three row engines: CSR with direct loads and L lanes per row (256 threads),
+// CSR with TMA-staged tiles (288 threads, dynamic shared memory), SELL-32-sigma (256 threads, a warp
+// per slice).
+template <int L, int ENG, class G, class E>
 __device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E &e, double &a0, double &a1) {
-  if constexpr (TMA) {
+  if constexpr (ENG == kEngTma) {
     extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
     spmv_rows_tma<L>(A.n, A.nnz, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
+  } else if constexpr (ENG == kEngSell) {
+    spmv_rows_sell(A.n, A.sell_slices, A.sell_off, A.sell_cols, A.sell_vals, A.sell_perm, A.sell_nlong, A.sell_long, A.sell_chunk, A.sell_warp_chunks, A.rowptr,
+                   A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
   } else {
     spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
   }
 }
-#define CGB_BOUNDS(TMA) __launch_bounds__((TMA) ? kTmaThreads : kBlock)
+#define CGB_BOUNDS(ENG) __launch_bounds__((ENG) == kEngTma ? kTmaThreads : kBlock)
 
 __device__ __forceinline__ bool cg_active(const CgState *st) {
   // reference: do { ... } while (counter++ < N && !*is_done)   (src/CG.hpp:436)
@@ -50,15 +64,15 @@ __device__ __forceinline__ bool cg_active(const CgState *st) {
 }
 
 // ---- K0 -------------------------------------------------------------------------------------
-template <int L, bool TMA>
-__global__ void CGB_BOUNDS(TMA) cg_init_kernel(CsrView A, const double *__restrict__ x,
+template <int L, int ENG>
+__global__ void CGB_BOUNDS(ENG) cg_init_kernel(CsrView A, const double *__restrict__ x,
                                                           const double *__restrict__ b, double *__restrict__ r,
                                                           CgState *st, double *partials, double *hist) {
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiInitResidual e{b, r};
-  spmv_rows<L, TMA>(A, g, e, a0, a1);
+  spmv_rows<L, ENG>(A, g, e, a0, a1);
   a0 = block_sum(a0, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = a0;
   if (publish_and_elect(&st->ticket, gridDim.x)) {
@@ -109,8 +123,8 @@ static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, co
 
 // ---- K1 -------------------------------------------------------------------------------------
 // FUSED: p buffers ping-pong on the iteration parity; p_old = pbuf[iter & 1], p_new = pbuf[~iter & 1].
-template <int L, bool TMA, bool FUSED>
-__global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
+template <int L, int ENG, bool FUSED>
+__global__ void CGB_BOUNDS(ENG) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
                                                           double *pbuf1, double *__restrict__ Ap, double *x,
                                                           CgState *st, double *partials, double *local_out) {
   if (!cg_active(st)) return;
@@ -123,11 +137,11 @@ __global__ void CGB_BOUNDS(TMA) cg_spmv_kernel(CsrView A, const double *__restri
     const double beta = st->beta;
     GatherFusedP g{r, p_old, beta};
     EpiDotFusedP e{Ap, r, p_old, p_new, x, beta, st->alpha};
-    spmv_rows<L, TMA>(A, g, e, a0, a1);
+    spmv_rows<L, ENG>(A, g, e, a0, a1);
   } else {
     GatherPlain g{pbuf0};
     EpiDotP e{Ap, pbuf0};
-    spmv_rows<L, TMA>(A, g, e, a0, a1);
+    spmv_rows<L, ENG>(A, g, e, a0, a1);
   }
   a0 = block_sum(a0, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = a0;
@@ -243,15 +257,15 @@ static __global__ void cg_advance_kernel(CgState *st, const double *rr_global, d
 }
 
 // ---- K4 -------------------------------------------------------------------------------------
-template <int L, bool TMA>
-__global__ void CGB_BOUNDS(TMA) residual_kernel(CsrView A, const double *__restrict__ x,
+template <int L, int ENG>
+__global__ void CGB_BOUNDS(ENG) residual_kernel(CsrView A, const double *__restrict__ x,
                                                            const double *__restrict__ b, double *out2,
                                                            double *partials, unsigned int *ticket) {
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiAccuracy e{b, x};
-  spmv_rows<L, TMA>(A, g, e, a0, a1);
+  spmv_rows<L, ENG>(A, g, e, a0, a1);
   a0 = block_sum(a0, red);
   a1 = block_sum(a1, red);
   if (threadIdx.x == 0) {
@@ -269,12 +283,12 @@ __global__ void CGB_BOUNDS(TMA) residual_kernel(CsrView A, const double *__restr
 }
 
 // y = A x (plain)
-template <int L, bool TMA>
-__global__ void CGB_BOUNDS(TMA) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
+template <int L, int ENG>
+__global__ void CGB_BOUNDS(ENG) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiStore e{y};
-  spmv_rows<L, TMA>(A, g, e, a0, a1);
+  spmv_rows<L, ENG>(A, g, e, a0, a1);
 }
 
 } // namespace cgb

@@ -34,6 +34,8 @@ int fail(int code, const char *fmt, ...);
     if (!(cond)) return ::cgb::fail(CGB_ERR_INVALID, "%s", msg);    \
   } while (0)
 
+constexpr int kEngVec = 0, kEngTma = 1, kEngSell = 2; // row engines of the SpMV-shaped kernels
+constexpr int kSellLongRow = 256; // rows longer than this stay out of the SELL slices (sell.cu)
 constexpr int kBlock = 256;        // threads per CTA for every streaming kernel
 constexpr int kMaxPartials = 4096; // upper bound on CTAs that take part in a reduction
 
@@ -69,6 +71,8 @@ struct cgb_ctx {
   int coop_ok = 0;
   size_t l2_bytes = 0;
   size_t l2_persist_max = 0;
+  size_t l2_window_max = 0;   // largest access-policy window the device accepts
+  size_t l2_persist_set = 0;  // persisting carve-out currently configured (cudaLimitPersistingL2CacheSize)
   cudaStream_t stream = nullptr;
   // scratch for the per-op reductions (lazy)
   double *partials = nullptr;

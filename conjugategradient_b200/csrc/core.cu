@@ -74,6 +74,7 @@ int cgb_ctx_create(int device, cgb_ctx **out) {
   ctx->coop_ok = prop.cooperativeLaunch;
   ctx->l2_bytes = (size_t)prop.l2CacheSize;
   ctx->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
+  ctx->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     delete ctx;

@@ -18,6 +18,8 @@ int csr_plan(cgb_csr *A) {
   A->lanes = lanes;
   const int sms = A->ctx->sm_count;
   A->grid_spmv = sms * 8;
+  A->grid_sell = sms * 8;
+  if ((A->n + 255) / 256 < A->grid_sell) A->grid_sell = (int)((A->n + 255) / 256 > 0 ? (A->n + 255) / 256 : 1);
   // streaming vector kernels: exactly one resident wave (grid-stride loops), so no partial second wave
   // leaves SMs idle at the tail; CGB_VEC_CTAS caps the CTAs per SM for A/B measurements
   int occ_u = 8, occ_p = 8;
@@ -50,6 +52,52 @@ int csr_plan(cgb_csr *A) {
   auto al16 = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
   const char *env = getenv("CGB_SPMV_ENGINE"); // "vec" forces direct loads (A/B measurements)
   A->use_tma = al16(A->vals) && al16(A->cols) && al16(A->rowptr) && ntiles >= 2 && !(env && !strcmp(env, "vec"));
+  return CGB_OK;
+}
+
+// max row length and number of TMA tiles that overflow a stage: one pass over the row offsets
+__global__ void csr_stats_kernel(int64_t n, const int *__restrict__ rowptr, int tile_rows, int cap, int *max_row,
+                                 unsigned long long *overflow) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int len = 0;
+  if (t < n) len = rowptr[t + 1] - rowptr[t];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) len = max(len, __shfl_xor_sync(0xffffffffu, len, o));
+  if ((threadIdx.x & 31) == 0 && len > 0) atomicMax(max_row, len);
+  if (t < n && t % tile_rows == 0) {
+    const int64_t e = t + tile_rows < n ? t + tile_rows : n;
+    if (rowptr[e] - rowptr[t] + 8 > cap) atomicAdd(overflow, 1ull);
+  }
+}
+
+constexpr int kSellDefaultSigma = 32768;
+
+int csr_prepare(cgb_csr *A) {
+  if (A->n == 0) return CGB_OK;
+  cgb_ctx *ctx = A->ctx;
+  if (!A->stats_done) {
+    int *d_max = nullptr;
+    CGB_CUDA(cudaMalloc(&d_max, 16));
+    CGB_CUDA(cudaMemsetAsync(d_max, 0, 16, ctx->stream));
+    const int tile_rows = kTmaConsumers / A->lanes_tma;
+    csr_stats_kernel<<<(unsigned)((A->n + 255) / 256), 256, 0, ctx->stream>>>(A->n, A->rowptr, tile_rows, kTmaCap, d_max,
+                                                                             (unsigned long long *)(d_max + 2));
+    int h[4] = {0, 0, 0, 0};
+    cudaError_t e = cudaMemcpyAsync(h, d_max, 16, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_max);
+    if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "csr_prepare: %s", cudaGetErrorString(e));
+    A->max_row = h[0];
+    memcpy(&A->overflow_tiles, h + 2, 8);
+    A->stats_done = true;
+    // CGB_FMT_AUTO: irregular row lengths (tiles that overflow the TMA stage, or a long tail) -> SELL-32-sigma
+    const double mean = (double)A->nnz / (double)A->n;
+    const int64_t ntiles = (A->n + tile_rows - 1) / tile_rows;
+    A->auto_sell = A->n >= 4096 && (A->overflow_tiles * 50 > ntiles || (double)A->max_row > 8.0 * mean + 64.0);
+    if (const char *env = getenv("CGB_AUTO_SELL")) A->auto_sell = atoi(env) != 0;
+  }
+  const bool want_sell = A->format == CGB_FMT_SELL || (A->format == CGB_FMT_AUTO && A->auto_sell);
+  if (want_sell && !A->sell_vals) CGB_TRY(cgb_csr_build_sell(A, kSellDefaultSigma));
   return CGB_OK;
 }
 
@@ -216,6 +264,8 @@ int cgb_csr_destroy(cgb_csr *A) {
   cudaFree(A->sell_cols);
   cudaFree(A->sell_off);
   cudaFree(A->sell_perm);
+  cudaFree(A->sell_long);
+  cudaFree(A->sell_chunk);
   if (A->owns) {
     cudaFree(A->vals);
     cudaFree(A->cols);
@@ -234,6 +284,11 @@ int32_t *cgb_csr_rowptr(cgb_csr *A) { return A ? A->rowptr : nullptr; }
 int cgb_csr_set_format(cgb_csr *A, int format) {
   CGB_REQUIRE(A, "cgb_csr_set_format: NULL matrix");
   CGB_REQUIRE(format == CGB_FMT_AUTO || format == CGB_FMT_CSR || format == CGB_FMT_SELL, "unknown format");
+  if (format == CGB_FMT_SELL && !A->sell_vals) CGB_TRY(cgb_csr_build_sell(A, kSellDefaultSigma));
+  if (format != A->format && A->ws.graph) { // cached graphs hold the other engine's kernels
+    cudaGraphExecDestroy(A->ws.graph);
+    A->ws.graph = nullptr;
+  }
   A->format = format;
   return CGB_OK;
 }
@@ -243,6 +298,7 @@ int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
   CGB_REQUIRE(ctx && A && d_x && d_y, "cgb_spmv: NULL argument");
   if (A->n == 0) return CGB_OK;
   ScopedDevice sd(ctx->device);
+  CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
   dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
     launch_kernel(spmv_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_y);
@@ -261,6 +317,7 @@ int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b,
     return CGB_OK;
   }
   double *out2 = ctx->partials + 2 * kMaxPartials - 2; // tail of the scratch is never a partial slot
+  CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
   dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
     launch_kernel(residual_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_b, out2,

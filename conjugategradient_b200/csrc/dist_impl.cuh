@@ -399,6 +399,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   int batch = o.check_every > 0 ? o.check_every : 32;
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
+  CGB_TRY(csr_prepare(A));
   CGB_TRY(workspace_ensure(A, n, false, hist_cap));
   Workspace &w = A->ws;
   const bool use_graph = o.loop_mode != CGB_LOOP_STEPWISE;
@@ -506,6 +507,7 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
   cgb_csr *A = d->Aloc;
   ScopedDevice sd(ctx->device);
   cudaStream_t s = ctx->stream;
+  CGB_TRY(csr_prepare(A));
   CGB_TRY(workspace_ensure(A, A->n, false, 0));
   Workspace &w = A->ws;
   CGB_TRY(halo_exchange(d, d_x, 0));

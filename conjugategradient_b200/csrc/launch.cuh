@@ -12,26 +12,38 @@ struct SpmvLaunch {
   int block;
   size_t smem;
   int lanes;
-  bool tma;
+  int tma; // engine: kEngVec / kEngTma / kEngSell (the name is kept from the two-engine days)
 };
+
+inline int csr_engine(const cgb_csr *A) {
+  if ((A->format == CGB_FMT_SELL || (A->format == CGB_FMT_AUTO && A->auto_sell)) && A->sell_vals) return kEngSell;
+  return A->use_tma ? kEngTma : kEngVec;
+}
 
 inline SpmvLaunch spmv_launch_cfg(const cgb_csr *A) {
   SpmvLaunch c;
-  c.tma = A->use_tma;
-  c.lanes = c.tma ? A->lanes_tma : A->lanes;
-  c.grid = c.tma ? A->grid_tma : A->grid_spmv;
-  c.block = c.tma ? kTmaThreads : kBlock;
-  c.smem = c.tma ? tma_smem_bytes(kTmaConsumers / c.lanes) : 0;
+  c.tma = csr_engine(A);
+  c.lanes = c.tma == kEngTma ? A->lanes_tma : (c.tma == kEngSell ? 1 : A->lanes);
+  c.grid = c.tma == kEngTma ? A->grid_tma : (c.tma == kEngSell ? A->grid_sell : A->grid_spmv);
+  c.block = c.tma == kEngTma ? kTmaThreads : kBlock;
+  c.smem = c.tma == kEngTma ? tma_smem_bytes(kTmaConsumers / c.lanes) : 0;
   return c;
 }
 
-inline CsrView csr_view(const cgb_csr *A) { return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals}; }
+inline CsrView csr_view(const cgb_csr *A) {
+  return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals, A->sell_slices, A->sell_off, A->sell_cols, A->sell_vals, A->sell_perm,
+                 A->sell_nlong, A->sell_long, A->sell_chunk, A->sell_warp_chunks};
+}
 
-// f(std::integral_constant<int, L>, std::bool_constant<TMA>)
-template <class F> inline void dispatch_lanes(int lanes, bool tma, F &&f) {
-#define CGB_CASE(LV)                                                  \
-  if (tma) f(std::integral_constant<int, LV>{}, std::true_type{});    \
-  else f(std::integral_constant<int, LV>{}, std::false_type{});       \
+// f(std::integral_constant<int, L>, std::integral_constant<int, ENG>)
+template <class F> inline void dispatch_lanes(int lanes, int eng, F &&f) {
+  if (eng == kEngSell) {
+    f(std::integral_constant<int, 1>{}, std::integral_constant<int, kEngSell>{});
+    return;
+  }
+#define CGB_CASE(LV)                                                                                   \
+  if (eng == kEngTma) f(std::integral_constant<int, LV>{}, std::integral_constant<int, kEngTma>{});    \
+  else f(std::integral_constant<int, LV>{}, std::integral_constant<int, kEngVec>{});                   \
   break;
   switch (lanes) {
   case 1: CGB_CASE(1)

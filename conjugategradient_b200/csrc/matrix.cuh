@@ -48,6 +48,12 @@ struct cgb_csr {
   bool use_tma = true; // TMA-staged row engine (spmv_tma.cuh) instead of direct loads
   int lanes_tma = 1;   // lanes per row of the TMA engine (tile = 256 / lanes_tma rows)
   int grid_tma = 0;
+  int grid_sell = 0;   // CTAs of the SELL engine (8 warps each, a warp per slice)
+  // row-length statistics (csr_stats, computed once on first use) and what CGB_FMT_AUTO makes of them
+  bool stats_done = false;
+  int max_row = 0;
+  int64_t overflow_tiles = 0; // TMA tiles whose non-zeros do not fit a pipeline stage (served by slow direct loads)
+  bool auto_sell = false;
   // SELL-C-sigma shadow copy
   int sell_sigma = 0;
   int64_t sell_slices = 0;
@@ -55,12 +61,17 @@ struct cgb_csr {
   double *sell_vals = nullptr;
   int32_t *sell_cols = nullptr;
   int64_t *sell_off = nullptr;  // slice offsets (in entries), sell_slices + 1
-  int32_t *sell_perm = nullptr; // slot -> row (NULL when sigma == 1)
+  int32_t *sell_perm = nullptr; // slot -> row, ~row for rows served from the long-row list (NULL: identity, no long rows)
+  int32_t *sell_long = nullptr; // rows longer than kSellLongRow: processed a warp per row from the CSR arrays
+  int64_t sell_nlong = 0;
+  int sell_warp_chunks = 1;
+  int64_t *sell_chunk = nullptr; // grid_sell + 1 slice offsets: CTA b streams slices [chunk[b], chunk[b+1]) (equal work)
   cgb::Workspace ws;
 };
 
 namespace cgb {
 int csr_plan(cgb_csr *A);
+int csr_prepare(cgb_csr *A); // before any SpMV-shaped launch: statistics, CGB_FMT_AUTO decision, lazy SELL build
 int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap);
 void workspace_release(cgb_csr *A);
 } // namespace cgb

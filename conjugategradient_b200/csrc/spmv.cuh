@@ -131,6 +131,90 @@ __device__ __forceinline__ void spmv_rows_vec(int64_t row_lo, int64_t row_hi, co
   }
 }
 
+
+// ---- SELL-32-sigma engine -------------------------------------------------------------------------
+// Shadow copy of the CSR matrix built by cgb_csr_build_sell (sell.cu): rows are sorted by length inside
+// windows of sigma rows, grouped in slices of 32 slots, every slice padded to its longest row and stored
+// column-major (entry j of slot l at off[s] + 32 j + l).  A warp owns a slice, lane l owns slot l: every
+// load of values / column indices is a fully coalesced 256 / 128-byte warp access whatever the row
+// lengths are, and a long row costs its slice only (sigma keeps rows of similar length together).  The
+// row sum is the reference's own left-to-right order (src/VectorOperations.hpp:455-462).  Padding entries
+// carry column -1 and are skipped (never multiplied: 0 * Inf would poison the sum).
+__device__ __forceinline__ double ld_stream_f64_ef(const double *p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ int ld_stream_s32_ef(const int *p, uint64_t pol) {
+  int v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+
+template <class G, class E>
+__device__ __forceinline__ void spmv_rows_sell(int64_t n, int64_t slices, const int64_t *__restrict__ off,
+                                               const int *__restrict__ cols, const double *__restrict__ vals,
+                                               const int *__restrict__ perm, int64_t nlong,
+                                               const int *__restrict__ long_rows, const int64_t *__restrict__ chunk,
+                                               int warp_chunks, const int *__restrict__ rowptr,
+                                               const int *__restrict__ ccols, const double *__restrict__ cvals, const G &g,
+                                               const E &e, int bid, int nb, double &a0, double &a1) {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_id = (int64_t)bid * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)nb * (blockDim.x >> 5);
+  // every warp (or CTA, whose warps then take slices round-robin) streams its own contiguous range of
+  // slices holding an equal share of the stored entries: static, deterministic, balanced by work
+  const int wpb = blockDim.x >> 5;
+  const int64_t unit = warp_chunks ? warp_id : (int64_t)bid;
+  const int64_t s_end = chunk[unit + 1];
+  const int64_t s_step = warp_chunks ? 1 : wpb;
+  for (int64_t s = chunk[unit] + (warp_chunks ? 0 : (threadIdx.x >> 5)); s < s_end; s += s_step) {
+    const int64_t o0 = off[s], o1 = off[s + 1];
+    double sum = 0.0;
+    int64_t j = o0 + lane;
+    for (; j + 96 < o1; j += 128) { // four column-major steps in flight
+      const int c0 = ld_stream_s32_ef(cols + j, pol), c1 = ld_stream_s32_ef(cols + j + 32, pol);
+      const int c2 = ld_stream_s32_ef(cols + j + 64, pol), c3 = ld_stream_s32_ef(cols + j + 96, pol);
+      const double v0 = ld_stream_f64_ef(vals + j, pol), v1 = ld_stream_f64_ef(vals + j + 32, pol);
+      const double v2 = ld_stream_f64_ef(vals + j + 64, pol), v3 = ld_stream_f64_ef(vals + j + 96, pol);
+      const double x0 = c0 >= 0 ? g(c0) : 0.0, x1 = c1 >= 0 ? g(c1) : 0.0;
+      const double x2 = c2 >= 0 ? g(c2) : 0.0, x3 = c3 >= 0 ? g(c3) : 0.0;
+      if (c0 >= 0) sum = fma(v0, x0, sum);
+      if (c1 >= 0) sum = fma(v1, x1, sum);
+      if (c2 >= 0) sum = fma(v2, x2, sum);
+      if (c3 >= 0) sum = fma(v3, x3, sum);
+    }
+    for (; j < o1; j += 32) {
+      const int c = ld_stream_s32_ef(cols + j, pol);
+      const double v = ld_stream_f64_ef(vals + j, pol);
+      if (c >= 0) sum = fma(v, g(c), sum);
+    }
+    const int64_t slot = s * 32 + lane;
+    if (slot < n) {
+      const int64_t row = perm ? (int64_t)perm[slot] : slot;
+      if (row >= 0) e.row(row, sum, a0, a1); // negative: a long row, handled below
+    }
+  }
+  // long rows: a warp per row over the CSR arrays (coalesced), two steps in flight, shuffle reduction
+  for (int64_t k = warp_id; k < nlong; k += nwarps) {
+    const int64_t row = long_rows[k];
+    const int b = __ldg(rowptr + row), en = __ldg(rowptr + row + 1);
+    double s0 = 0.0, s1 = 0.0;
+    int j = b + lane;
+    for (; j + 32 < en; j += 64) {
+      const int c0 = ld_stream_s32_ef(ccols + j, pol), c1 = ld_stream_s32_ef(ccols + j + 32, pol);
+      const double v0 = ld_stream_f64_ef(cvals + j, pol), v1 = ld_stream_f64_ef(cvals + j + 32, pol);
+      s0 = fma(v0, g(c0), s0);
+      s1 = fma(v1, g(c1), s1);
+    }
+    if (j < en) s0 = fma(ld_stream_f64_ef(cvals + j, pol), g(ld_stream_s32_ef(ccols + j, pol)), s0);
+    double sum = warp_sum(s0 + s1);
+    if (lane == 0) e.row(row, sum, a0, a1);
+  }
+}
+
 template <class G, class E>
 __device__ __forceinline__ void spmv_rows_dispatch(int lanes, int64_t row_lo, int64_t row_hi, const int *rowptr,
                                                    const int *cols, const double *vals, const G &g, const E &e,

@@ -140,6 +140,14 @@ class Matrix:
         L.check(ctx.lib.cgb_gen_stencil(ctx.h, k, m, mz, row_begin, row_end, C.byref(h)))
         return cls(ctx, handle=h)
 
+    @classmethod
+    def random_spd(cls, ctx: Context, n: int, seed: int = 12345, d_min: int = 2, d_max: int = 4096, gamma: float = 2.2,
+                   row_begin: int = 0, row_end: int = -1):
+        """Random SPD matrix with power-law row lengths generated on the device (config C5)."""
+        h = C.c_void_p()
+        L.check(ctx.lib.cgb_gen_random_spd(ctx.h, n, seed, d_min, d_max, gamma, row_begin, row_end, C.byref(h)))
+        return cls(ctx, handle=h)
+
     def N(self) -> int:
         return int(self.ctx.lib.cgb_csr_n(self.h))
 
@@ -155,10 +163,14 @@ class Matrix:
         L.check(lib.cgb_memcpy_d2h(c, _p(rows), lib.cgb_csr_rowptr(self.h), 4 * (n + 1), 1))
         return vals, cols, rows
 
-    def set_format(self, fmt: int, sigma: int = 1):
-        if fmt == L.FMT_SELL:
+    def set_format(self, fmt: int, sigma: int | None = None):
+        """sigma: SELL sorting window (None: keep the copy already built, or the library default)."""
+        if fmt == L.FMT_SELL and sigma is not None:
             L.check(self.ctx.lib.cgb_csr_build_sell(self.h, sigma))
         L.check(self.ctx.lib.cgb_csr_set_format(self.h, fmt))
+
+    def sell_padded(self) -> int:
+        return int(self.ctx.lib.cgb_csr_sell_padded(self.h))
 
     def free(self):
         if self.h:

@@ -98,7 +98,12 @@ int32_t *cgb_csr_rowptr(cgb_csr *A); /* Matrix::rows_ptr()    (:86) */
 /* Build the SELL-C-sigma shadow copy used by the SpMV when format == CGB_FMT_SELL
  * (C = 32 rows per slice; sigma = sorting window in rows, 1 = no permutation). */
 int cgb_csr_build_sell(cgb_csr *A, int sigma);
-/* Selects the storage the SpMV streams: CGB_FMT_AUTO picks by row-length statistics. */
+/* Stored entries of the SELL copy including padding (0 before cgb_csr_build_sell). */
+int64_t cgb_csr_sell_padded(const cgb_csr *A);
+/* Selects the storage the SpMV-shaped kernels stream.  CGB_FMT_AUTO and CGB_FMT_CSR use the caller's CSR
+ * arrays as they are (TMA-staged tiles); CGB_FMT_AUTO switches to the SELL copy when the row lengths are
+ * irregular (tiles that overflow a TMA stage, or a long tail); CGB_FMT_SELL builds the SELL copy on first
+ * use (sigma = 32768) unless cgb_csr_build_sell was called with another window. */
 enum { CGB_FMT_AUTO = 0, CGB_FMT_CSR = 1, CGB_FMT_SELL = 2 };
 int cgb_csr_set_format(cgb_csr *A, int format);
 int cgb_csr_get_format(const cgb_csr *A);
@@ -110,6 +115,14 @@ int cgb_csr_get_format(const cgb_csr *A);
  * stay GLOBAL.  Pass row_begin = 0, row_end = -1 for the whole matrix. */
 int cgb_gen_stencil(cgb_ctx *ctx, int kind, int64_t m, int64_t mz, int64_t row_begin, int64_t row_end,
                     cgb_csr **out);
+
+/* On-device generation of the random SPD matrix with power-law row lengths:
+ * strictly-lower degree of row i = min(d_max, floor(d_min * u^(-1/(gamma-1)))) capped at i, distinct
+ * columns (one per stratum of [0, i)), values in (-1, 0), mirrored, a_ii = 1 + sum |a_ij|.
+ * Deterministic in (n, seed, d_min, d_max, gamma).  Rows [row_begin, row_end) with GLOBAL columns
+ * (row_begin = 0, row_end = -1: the whole matrix). */
+int cgb_gen_random_spd(cgb_ctx *ctx, int64_t n, uint64_t seed, int d_min, int d_max, double gamma, int64_t row_begin,
+                       int64_t row_end, cgb_csr **out);
 
 /* ---- per-op kernels ------------------------------------------------------------------------
  * Scalar operands are DEVICE pointers dereferenced at kernel run time, and reductions ADD INTO

@@ -1,0 +1,49 @@
+"""C5 probe: random SPD n rows on the device, CSR-TMA vs SELL engines.  python tools/c5_probe.py [n]"""
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from conjugategradient_b200 import _lib as L  # noqa: E402
+from conjugategradient_b200 import solver as S  # noqa: E402
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
+    ctx = S.Context(0)
+    t0 = time.time()
+    A = S.Matrix.random_spd(ctx, n)
+    ctx.sync()
+    nnz = A.NNZ()
+    print(f"generated n={n} nnz={nnz} mean={nnz / n:.2f} in {time.time() - t0:.2f}s", flush=True)
+    b = np.arange(1, n + 1, dtype=np.float64)
+    tol = 1e-8 * float(np.sqrt(n * (n + 1) * (2 * n + 1) / 6.0))
+    B_iter = 12 * nnz + 4 * (n + 1) + 88 * n
+    cfgs = os.environ.get("C5_CONFIGS", "csr:0,sell:1,sell:1024,sell:4096,sell:32768,sell:262144")
+    for fmt, sigma in [((L.FMT_SELL if a == "sell" else L.FMT_CSR), int(b_)) for a, b_ in (c.split(":") for c in cfgs.split(","))]:
+        A.set_format(L.FMT_CSR)
+        if fmt == L.FMT_SELL:
+            t0 = time.time()
+            L.check(ctx.lib.cgb_csr_build_sell(A.h, sigma))
+            ctx.sync()
+            tb = time.time() - t0
+            A.set_format(L.FMT_SELL)
+        for fused in (0,):
+            cg = S.CG(ctx, fuse_p_update=fused, time_kernels=1)
+            cg.setMatrix(A)
+            cg.setTarget(b)
+            cg.solve(tol)
+            cg.x = None
+            st = cg.solve(tol)
+            sec = st["solve_ms"] / 1e3
+            it = st["iterations"]
+            rr, xx = cg.residual()
+            extra = f" sell_padded={A.sell_padded() / nnz:.3f}x build={tb:.2f}s sigma={sigma}" if fmt == L.FMT_SELL else ""
+            print(f"fmt={'SELL' if fmt == L.FMT_SELL else 'CSR '} fused={fused} it={it} {it / sec:8.1f} it/s {it * B_iter / sec / 1e9:7.1f} GB/s(B_iter) "
+                  f"spmv {st['spmv_ms']:.4f} ms true_rel_res={np.sqrt(rr) / (tol / 1e-8):.2e}{extra}", flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -264,7 +264,8 @@ def run_ours(args, kind, m, rel):
     tol = rel * nb
     bvec = S.Vector(ctx, b_host)
     xvec = S.Vector(ctx, n=nloc)
-    opts = S.make_opts(time_kernels=1 if world == 1 else 0, check_every=args.check_every)
+    small = n <= 131072  # latency regime: the library's AUTO loop is the persistent cooperative kernel (one launch per solve)
+    opts = S.make_opts(time_kernels=1 if (world == 1 and not small) else 0, check_every=args.check_every)
     stats = L.CgStats()
 
     dh = None
@@ -350,6 +351,15 @@ def run_ours(args, kind, m, rel):
     # ---- roofline of the dominant kernel (SpMV + p.Ap), timed live with CUDA events ----------------
     peak, peak_src = measured_peak()
     roof = None
+    if last["loop_mode"] == L.LOOP_PERSISTENT:
+        # one cooperative kernel runs the whole solve: its launch = all iterations (bandwidth fraction is not meaningful
+        # at this size -- 2.5 MB per iteration lives in L2; the figure of merit is microseconds per iteration)
+        by = last["iterations"] * b_iter(n, nnz)
+        ms1 = ms_total / args.steps
+        roof = {"bound": "hbm", "kernel": "cg_persistent_kernel (whole CG loop, cooperative launch)", "achieved": by / (ms1 * 1e6),
+                "peak": peak, "unit": "GB/s", "frac": by / (ms1 * 1e6) / peak, "peak_source": peak_src, "traffic": None,
+                "bytes_per_launch": by, "ms_per_launch": ms1, "share_of_iteration": 1.0,
+                "us_per_iteration": 1e3 * ms_total / max(iters, 1), "regime": "latency-bound (working set in L2)"}
     spmv = [o["spmv_ms"] for o in outs if o["timed_samples"] > 0]
     if spmv:
         k1_bytes = 12 * nnz + 4 * (n + 1) + 16 * n  # vals + cols + rowptr + p read + Ap write
@@ -440,7 +450,8 @@ def run_ours(args, kind, m, rel):
             "config": config_dict(args.workload, kind, m, n, nnz, rel, f"{world}xB200",
                                   parallelism=f"row-partitioned x{world}" if world > 1 else "single GPU",
                                   iterations_per_solve=last["iterations"], true_rel_residual=true_rel,
-                                  loop="CUDA graph batches of %d iterations, device-side stop flag" % args.check_every,
+                                  loop=("one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT
+                                        else "CUDA graph batches of %d iterations, device-side stop flag" % args.check_every),
                                   engine="SELL-32-sigma" if last["format"] == L.FMT_SELL else "CSR TMA-staged",
                                   transport=(os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None)),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

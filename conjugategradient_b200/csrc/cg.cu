@@ -3,6 +3,7 @@
 // 12 device operations and one wait_and_throw per iteration; here a batch of iterations is one
 // CUDA-graph launch and the stop flag lives on the device, polled once per batch.
 #include "launch.cuh"
+#include "persistent.cuh"
 
 #include <algorithm>
 #include <vector>
@@ -139,12 +140,18 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   cudaStream_t s = ctx->stream;
 
   int mode = o.loop_mode;
-  if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = CGB_LOOP_GRAPH;
   int batch = o.check_every > 0 ? o.check_every : 32;
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
-  const bool fused = o.fuse_p_update != 0;
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
   CGB_TRY(csr_prepare(A));
+  // One cooperative kernel for the whole loop (persistent.cuh) when asked for, or, under AUTO, when the
+  // system is small enough that latency rules (CGB_PERSISTENT_MAX_N rows); it serves CSR rows only.
+  int64_t persistent_max_n = 131072; // measured cross-over on B200: 2D 5-pt 256^2 still wins (89k vs 77k it/s), 512^2 loses
+  if (const char *e = getenv("CGB_PERSISTENT_MAX_N")) persistent_max_n = atoll(e);
+  const bool can_persist = ctx->coop_ok && csr_engine(A) != kEngSell && !o.time_kernels;
+  const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
+  if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
+  const bool fused = o.fuse_p_update != 0 || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
   // L2 window: explicit option, or CGB_L2_WINDOW=1/0; only meaningful without the fused p-update (p ping-pongs there)
@@ -214,6 +221,32 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const int per_iter = fused ? 2 : 3;
   double t_p = 0, t_s = 0, t_u = 0;
   int64_t samples = 0;
+  if (persistent) {
+    int rc = CGB_OK;
+    dispatch_lanes(A->lanes, kEngVec, [&](auto Lc, auto) {
+      constexpr int L = decltype(Lc)::value;
+      auto kernel = cg_persistent_kernel<L>;
+      int occ = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kBlock, 0) != cudaSuccess || occ < 1) {
+        rc = fail(CGB_ERR_CUDA, "cg_persistent_kernel: occupancy query failed");
+        return;
+      }
+      // as many CTAs as one pass over the rows needs, never more than can be co-resident
+      const int64_t rows_per_cta = (int64_t)(kBlock / L) * 2;
+      int grid = (int)std::min<int64_t>((int64_t)occ * ctx->sm_count, (n + rows_per_cta - 1) / rows_per_cta);
+      if (const char *e = getenv("CGB_PERSISTENT_CTAS")) grid = std::min(grid, std::max(1, atoi(e)));
+      if (grid < 1) grid = 1;
+      if (grid > kMaxPartials) grid = kMaxPartials;
+      CsrView V = csr_view(A);
+      double *xp = d_x, *rp = w.r, *p0 = w.p0, *p1 = w.p1, *ap = w.Ap, *parts = w.partials, *hist = w.hist;
+      CgState *stp = w.st;
+      void *args[] = {&V, &xp, &rp, &p0, &p1, &ap, &stp, &parts, &hist};
+      cudaError_t e = cudaLaunchCooperativeKernel((void *)kernel, dim3(grid), dim3(kBlock), args, 0, s);
+      if (e != cudaSuccess) rc = fail(CGB_ERR_CUDA, "cudaLaunchCooperativeKernel: %s", cudaGetErrorString(e));
+    });
+    CGB_TRY(rc);
+    launches += 1;
+  }
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
                          (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.tma << 2) ^
@@ -229,7 +262,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const bool pipelined = !cfg.time_kernels;
   int64_t issued = 0; // iterations issued so far
   int slot = 0;
-  bool finished = false;
+  bool finished = persistent; // the cooperative kernel has run the whole loop already
   bool have_prev = false;
   bool prev_active_at_start = true;
   while (!finished) {
@@ -270,9 +303,11 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     slot ^= 1;
   }
   // the x update of the last trip (deferred: see cg_kernels.cuh), then drain and take the final state
-  cg_xflush_kernel<<<cfg.grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, fused ? 1 : 0, w.st);
-  CGB_CUDA(cudaGetLastError());
-  launches += 1;
+  if (!persistent) {
+    cg_xflush_kernel<<<cfg.grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, fused ? 1 : 0, w.st);
+    CGB_CUDA(cudaGetLastError());
+    launches += 1;
+  }
   CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
   CGB_CUDA(cudaEventRecord(t1, s));
   CGB_CUDA(cudaEventSynchronize(t1));

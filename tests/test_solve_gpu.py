@@ -20,11 +20,13 @@ SOLVES = sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if os.path.bas
 
 X_RTOL = 1e-10
 VARIANTS = {
-    "graph": dict(),
-    "graph_fused": dict(fuse_p_update=1),
+    "auto": dict(),                                   # small systems: the persistent cooperative kernel
+    "persistent": dict(loop_mode=L.LOOP_PERSISTENT),
+    "graph": dict(loop_mode=L.LOOP_GRAPH),
+    "graph_fused": dict(loop_mode=L.LOOP_GRAPH, fuse_p_update=1),
     "stepwise": dict(loop_mode=L.LOOP_STEPWISE, check_every=5),
     "stepwise_fused": dict(loop_mode=L.LOOP_STEPWISE, fuse_p_update=1, check_every=1),
-    "graph_timed": dict(time_kernels=1, check_every=8),
+    "graph_timed": dict(loop_mode=L.LOOP_GRAPH, time_kernels=1, check_every=8),
 }
 
 
@@ -74,16 +76,22 @@ CASES = {
 }
 
 
-@pytest.mark.parametrize("fused", [0, 1])
+MODES = {"graph": dict(loop_mode=L.LOOP_GRAPH), "graph_fused": dict(loop_mode=L.LOOP_GRAPH, fuse_p_update=1),
+         "persistent": dict(loop_mode=L.LOOP_PERSISTENT)}
+
+
+@pytest.mark.parametrize("mode", sorted(MODES))
 @pytest.mark.parametrize("name", sorted(CASES))
-def test_solve_vs_oracle(ctx, port, name, fused):
+def test_solve_vs_oracle(ctx, port, name, mode):
     gen, rel = CASES[name]
     v, c, r = gen()
     n = r.size - 1
     b = G.default_rhs(n)
     tol = rel * np.linalg.norm(b)
     o = port.cg_solve(v, c, r, b, tol, history=True)
-    cg, st = run(ctx, v, c, r, b, tol, fuse_p_update=fused, record_history=1)
+    cg, st = run(ctx, v, c, r, b, tol, record_history=1, **MODES[mode])
+    if mode == "persistent" and not name.startswith("rspd"):   # (irregular rows go to the SELL engine, graph loop)
+        assert st["loop_mode"] == L.LOOP_PERSISTENT and st["kernel_launches"] == 2
     if name.startswith("rspd"):
         # Trip counts of this matrix class (eigenvalues spread over 3 decades) depend on the summation
         # order: the reference's own serial and OpenMP CPU builds give 364 and 356 trips here (2.2 %).

@@ -24,7 +24,7 @@ def main():
             tl = [int(c) for c in os.environ.get("PROBE_TIMED", "01")]
             for fused in fl:
                 for timed in tl:
-                    cg = S.CG(ctx, fuse_p_update=fused, time_kernels=timed, check_every=25)
+                    cg = S.CG(ctx, fuse_p_update=fused, time_kernels=timed, check_every=25, loop_mode=int(os.environ.get("PROBE_LOOP", "1")))
                     cg.setMatrix(A)
                     cg.setTarget(b)
                     cg.solve(0.0, max_iter=50)  # warm-up (graph build)

@@ -76,6 +76,7 @@ int nccl_load() {
 } // namespace
 
 namespace cgb {
+constexpr int64_t kHaloEngineMinNnz = 1 << 20; // below this the one-pass halo kernel is used
 struct PeerSend { // where the entries of the packed send list go: slice q -> dst[q][0 .. soff[q+1]-soff[q])
   long long soff[kMaxRanks + 1];
   double *dst[kMaxRanks];
@@ -385,6 +386,61 @@ __global__ void __launch_bounds__(kBlock) peer_halo_kernel(int64_t nh, const int
   }
 }
 
+// Same job as peer_halo_kernel, for halo parts that are a real share of the matrix (irregular matrices:
+// at 8 ranks 7/8 of a random row block's entries are remote): A_halo goes through the regular row
+// engines (TMA-staged CSR tiles or SELL slices) with the halo buffer as the gathered vector.
+struct GatherCg { // coherent at L2: the halo buffer is written by peers until the flags are up
+  const double *x;
+  __device__ __forceinline__ double operator()(int c) const { return __ldcg(x + c); }
+};
+struct EpiHaloAdd { // y[rows[k]] += s ; acc0 += p[rows[k]] * s
+  double *y;
+  const double *p;
+  const int *rows;
+  __device__ __forceinline__ void row(int64_t k, double s, double &a0, double &) const {
+    const int r = rows[k];
+    y[r] += s;
+    if (p) a0 = fma(p[r], s, a0);
+  }
+};
+
+template <int L, int ENG, int MODE>
+__global__ void CGB_BOUNDS(ENG) peer_halo_engine_kernel(CsrView H, const int *__restrict__ halo_rows, const double *halo,
+                                                        double *y, const double *p, const double *base, PeerCtx pc, PeerRecv pr,
+                                                        CgState *st, int gated, double *partials) {
+  if (gated && !cg_active(st)) return;
+  __shared__ double red[32];
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if (threadIdx.x < pc.nranks && pr.from[threadIdx.x]) {
+    if (!peer_wait(&pc.win[pc.rank]->hflag[threadIdx.x], pc.seq->halo)) s_ok = 0;
+  }
+  __syncthreads();
+  double a0 = 0.0, a1 = 0.0;
+  if (s_ok) { // uniform over the CTA: the engines synchronise inside
+    GatherCg g{halo};
+    EpiHaloAdd e{y, MODE == 1 ? p : nullptr, halo_rows};
+    spmv_rows<L, ENG>(H, g, e, a0, a1);
+  } else if (threadIdx.x == 0) {
+    peer_fail(st);
+  }
+  if (MODE == 1) {
+    a0 = block_sum(a0, red);
+    if (threadIdx.x == 0) partials[blockIdx.x] = a0;
+    if (publish_and_elect(&st->ticket, gridDim.x)) {
+      const double corr = reduce_partials(partials, gridDim.x, red);
+      bool ok = true;
+      const double pAp = peer_allreduce(pc, base[0] + corr, &ok);
+      if (threadIdx.x == 0) {
+        if (!ok) peer_fail(st);
+        st->pAp = pAp;
+        st->alpha = st->rr / pAp;
+      }
+    }
+  }
+}
+
 // K2 with the r.r all-reduce and the state advance in the last CTA.
 __global__ void __launch_bounds__(kBlock) peer_update_kernel(int64_t n, double *__restrict__ r,
                                                               const double *__restrict__ Ap, CgState *st,
@@ -515,7 +571,26 @@ int peer_halo_apply(cgb_dist *d, double *y, const double *p, const double *base,
   cudaStream_t s = d->ctx->stream;
   Workspace &w = d->Aloc->ws;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->nh + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 4));
-  const cgb_csr *H = d->Ahalo;
+  cgb_csr *H = d->Ahalo;
+  int64_t engine_min = kHaloEngineMinNnz;
+  if (const char *e = getenv("CGB_HALO_ENGINE_MIN")) engine_min = atoll(e);
+  if (H->nnz >= engine_min && H->n > 0) { // a real share of the matrix: regular row engines over A_halo
+    const SpmvLaunch lc = spmv_launch_cfg(H);
+    const CsrView V = csr_view(H);
+    const PeerCtx pc = d->pctx();
+    const PeerRecv pr = d->recv;
+    const int *hr = d->halo_rows;
+    const double *hb = d->halo;
+    CgState *stp = w.st;
+    double *parts = w.partials;
+    dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+      constexpr int LL = decltype(Lc)::value, EE = decltype(Tc)::value;
+      if (mode == 1) launch_kernel(peer_halo_engine_kernel<LL, EE, 1>, lc, s, V, hr, hb, y, p, base, pc, pr, stp, gated, parts);
+      else launch_kernel(peer_halo_engine_kernel<LL, EE, 0>, lc, s, V, hr, hb, y, p, base, pc, pr, stp, gated, parts);
+    });
+    CGB_CUDA(cudaGetLastError());
+    return CGB_OK;
+  }
   if (mode == 1)
     peer_halo_kernel<1><<<grid, kBlock, 0, s>>>(d->nh, H->rowptr, H->cols, H->vals, d->halo_rows, d->halo, y, p, base,
                                                 d->pctx(), d->recv, w.st, gated, w.partials);

@@ -400,6 +400,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
   CGB_TRY(csr_prepare(A));
+  if (d->Ahalo) CGB_TRY(csr_prepare(d->Ahalo));
   CGB_TRY(workspace_ensure(A, n, false, hist_cap));
   Workspace &w = A->ws;
   const bool use_graph = o.loop_mode != CGB_LOOP_STEPWISE;
@@ -496,7 +497,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     stats->solve_ms = ms;
     stats->kernel_launches = launches;
     stats->loop_mode = use_graph ? CGB_LOOP_GRAPH : CGB_LOOP_STEPWISE;
-    stats->format = CGB_FMT_CSR;
+    stats->format = csr_engine(A) == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
   }
   return CGB_OK;
 }
@@ -508,6 +509,7 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
   ScopedDevice sd(ctx->device);
   cudaStream_t s = ctx->stream;
   CGB_TRY(csr_prepare(A));
+  if (d->Ahalo) CGB_TRY(csr_prepare(d->Ahalo));
   CGB_TRY(workspace_ensure(A, A->n, false, 0));
   Workspace &w = A->ws;
   CGB_TRY(halo_exchange(d, d_x, 0));

@@ -11,12 +11,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("variant", ["default", "halo_engine", "nccl"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_dist_solve_matches_oracle(world):
+def test_dist_solve_matches_oracle(world, variant):
     if L.load().cgb_device_count() < world:
         pytest.skip(f"needs {world} GPUs")
+    env = dict(os.environ)
+    if variant == "halo_engine":
+        env["CGB_HALO_ENGINE_MIN"] = "1"      # A_halo through the regular row engines even for these small cases
+    if variant == "nccl":
+        env["CGB_DIST_TRANSPORT"] = "nccl"    # the fallback transport stays correct
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(29610 + world), os.path.join(ROOT, "tests", "dist_worker.py")]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
     assert out.stdout.count("DIST_OK") == 4 and "DIST_FAIL" not in out.stdout, out.stdout

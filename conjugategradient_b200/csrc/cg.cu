@@ -49,7 +49,7 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
   CGB_CUDA(mark(0));
   if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_CUDA(mark(1));
-  dispatch_lanes(c.sl.lanes, c.sl.tma, [&](auto Lc, auto Tc) {
+  dispatch_lanes(c.sl.lanes, c.sl.eng, [&](auto Lc, auto Tc) {
     constexpr int L = decltype(Lc)::value;
     constexpr int T = decltype(Tc)::value;
     if (c.fused)
@@ -211,7 +211,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
   CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)n, s));
   if (fused) CGB_CUDA(cudaMemsetAsync(w.p1, 0, sizeof(double) * (size_t)n, s));
-  dispatch_lanes(cfg.sl.lanes, cfg.sl.tma, [&](auto Lc, auto Tc) {
+  dispatch_lanes(cfg.sl.lanes, cfg.sl.eng, [&](auto Lc, auto Tc) {
     launch_kernel(cg_init_kernel<decltype(Lc)::value, decltype(Tc)::value>, cfg.sl, s, csr_view(A), (const double *)d_x,
                   d_b, w.r, w.st, w.partials, w.hist);
   });
@@ -249,7 +249,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   }
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
-                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.tma << 2) ^
+                         (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.eng << 2) ^
                          ((uint64_t)cfg.l2_window << 4);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
@@ -330,7 +330,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     }
     stats->kernel_launches = launches;
     stats->loop_mode = mode;
-    stats->format = cfg.sl.tma == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
+    stats->format = cfg.sl.eng == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
   }
   return CGB_OK;
 }

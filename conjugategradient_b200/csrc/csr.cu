@@ -300,7 +300,7 @@ int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
   ScopedDevice sd(ctx->device);
   CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
-  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+  dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
     launch_kernel(spmv_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_y);
   });
   CGB_CUDA(cudaGetLastError());
@@ -319,7 +319,7 @@ int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b,
   double *out2 = ctx->partials + 2 * kMaxPartials - 2; // tail of the scratch is never a partial slot
   CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
-  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+  dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
     launch_kernel(residual_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_b, out2,
                   ctx->partials, ctx->ticket);
   });

@@ -583,7 +583,7 @@ int peer_halo_apply(cgb_dist *d, double *y, const double *p, const double *base,
     const double *hb = d->halo;
     CgState *stp = w.st;
     double *parts = w.partials;
-    dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+    dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
       constexpr int LL = decltype(Lc)::value, EE = decltype(Tc)::value;
       if (mode == 1) launch_kernel(peer_halo_engine_kernel<LL, EE, 1>, lc, s, V, hr, hb, y, p, base, pc, pr, stp, gated, parts);
       else launch_kernel(peer_halo_engine_kernel<LL, EE, 0>, lc, s, V, hr, hb, y, p, base, pc, pr, stp, gated, parts);

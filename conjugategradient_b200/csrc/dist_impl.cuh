@@ -299,7 +299,7 @@ int dist_enqueue_iteration(cgb_dist *d, double *x) {
   const SpmvLaunch lc = spmv_launch_cfg(A);
   cg_pupdate_kernel<<<A->grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_TRY(halo_exchange(d, w.p0, 1));
-  dispatch_lanes(lc.lanes, lc.tma, [&](auto Lc, auto Tc) {
+  dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
     launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
                   w.p1, w.Ap, x, w.st, w.partials, d->scal + 0);
   });

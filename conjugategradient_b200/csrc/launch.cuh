@@ -12,7 +12,7 @@ struct SpmvLaunch {
   int block;
   size_t smem;
   int lanes;
-  int tma; // engine: kEngVec / kEngTma / kEngSell (the name is kept from the two-engine days)
+  int eng; // row engine: kEngVec / kEngTma / kEngSell
 };
 
 inline int csr_engine(const cgb_csr *A) {
@@ -22,11 +22,11 @@ inline int csr_engine(const cgb_csr *A) {
 
 inline SpmvLaunch spmv_launch_cfg(const cgb_csr *A) {
   SpmvLaunch c;
-  c.tma = csr_engine(A);
-  c.lanes = c.tma == kEngTma ? A->lanes_tma : (c.tma == kEngSell ? 1 : A->lanes);
-  c.grid = c.tma == kEngTma ? A->grid_tma : (c.tma == kEngSell ? A->grid_sell : A->grid_spmv);
-  c.block = c.tma == kEngTma ? kTmaThreads : kBlock;
-  c.smem = c.tma == kEngTma ? tma_smem_bytes(kTmaConsumers / c.lanes) : 0;
+  c.eng = csr_engine(A);
+  c.lanes = c.eng == kEngTma ? A->lanes_tma : (c.eng == kEngSell ? 1 : A->lanes);
+  c.grid = c.eng == kEngTma ? A->grid_tma : (c.eng == kEngSell ? A->grid_sell : A->grid_spmv);
+  c.block = c.eng == kEngTma ? kTmaThreads : kBlock;
+  c.smem = c.eng == kEngTma ? tma_smem_bytes(kTmaConsumers / c.lanes) : 0;
   return c;
 }
 

@@ -105,8 +105,9 @@ def measured_peak():
 def ncu_traffic(workload):
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
-        return json.load(open(p)).get(workload)
-    return None
+        t = json.load(open(p)).get(workload)
+        return (t["bytes_per_launch"], t.get("source")) if t else (None, None)
+    return None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -367,7 +368,8 @@ def run_ours(args, kind, m, rel):
         ach = k1_bytes / (k1_ms * 1e6)
         eng = "SELL-32-sigma copy, warp per slice" if last["format"] == L.FMT_SELL else "CSR, TMA-staged tiles"
         roof = {"bound": "hbm", "kernel": f"cg_spmv_kernel (SpMV + p.Ap; {eng})", "achieved": ach, "peak": peak,
-                "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "traffic": ncu_traffic(args.workload),
+                "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "traffic": ncu_traffic(args.workload)[0],
+                "traffic_source": ncu_traffic(args.workload)[1],
                 "bytes_per_launch": k1_bytes, "ms_per_launch": k1_ms,
                 "share_of_iteration": k1_ms / (ms_total / max(iters, 1)),
                 "update_ms": float(np.mean([o["update_ms"] for o in outs])),

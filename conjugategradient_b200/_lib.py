@@ -81,6 +81,8 @@ SIGNATURES = {
     "cgb_csr_sell_padded": (c_i64, [c_vp]),
     "cgb_csr_set_format": (C.c_int, [c_vp, C.c_int]),
     "cgb_csr_get_format": (C.c_int, [c_vp]),
+    "cgb_csr_set_panels": (C.c_int, [c_vp, C.c_int]),
+    "cgb_csr_get_panels": (C.c_int, [c_vp]),
     "cgb_gen_stencil": (C.c_int, [c_vp, C.c_int, c_i64, c_i64, c_i64, c_i64, C.POINTER(c_vp)]),
     "cgb_gen_random_spd": (C.c_int, [c_vp, c_i64, C.c_uint64, C.c_int, C.c_int, C.c_double, c_i64, c_i64, C.POINTER(c_vp)]),
     "cgb_spmv": (C.c_int, [c_vp, c_vp, c_vp, c_vp]),

@@ -42,13 +42,14 @@ struct LoopCfg {
 // (legal inside stream capture; they become event-record nodes of the graph).
 static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream_t s, bool timed) {
   Workspace &w = A->ws;
-  const CsrView V = csr_view(A);
+  const CsrView V = csr_view_final(A, w.Ap);
   auto mark = [&](int i) -> cudaError_t {
     return timed ? cudaEventRecordWithFlags(w.ev[i], s, cudaEventRecordExternal) : cudaSuccess;
   };
   CGB_CUDA(mark(0));
   if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_CUDA(mark(1));
+  launch_panel_partials(A, c.sl, s, w.p0, w.Ap, w.st); // column panels 0 .. P-2: Ap accumulates
   dispatch_lanes(c.sl.lanes, c.sl.eng, [&](auto Lc, auto Tc) {
     constexpr int L = decltype(Lc)::value;
     constexpr int T = decltype(Tc)::value;
@@ -151,7 +152,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const bool can_persist = ctx->coop_ok && csr_engine(A) != kEngSell && !o.time_kernels;
   const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
   if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
-  const bool fused = o.fuse_p_update != 0 || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
+  const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
   // L2 window: explicit option, or CGB_L2_WINDOW=1/0; only meaningful without the fused p-update (p ping-pongs there)
@@ -211,14 +212,16 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
   CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)n, s));
   if (fused) CGB_CUDA(cudaMemsetAsync(w.p1, 0, sizeof(double) * (size_t)n, s));
+  const int64_t extra = csr_panels(A) > 0 ? (int64_t)csr_panels(A) - 1 : 0; // partial launches per SpMV-shaped pass
+  launch_panel_partials(A, cfg.sl, s, d_x, w.r, nullptr); // r doubles as the accumulator of K0
   dispatch_lanes(cfg.sl.lanes, cfg.sl.eng, [&](auto Lc, auto Tc) {
-    launch_kernel(cg_init_kernel<decltype(Lc)::value, decltype(Tc)::value>, cfg.sl, s, csr_view(A), (const double *)d_x,
-                  d_b, w.r, w.st, w.partials, w.hist);
+    launch_kernel(cg_init_kernel<decltype(Lc)::value, decltype(Tc)::value>, cfg.sl, s, csr_view_final(A, w.r),
+                  (const double *)d_x, d_b, w.r, w.st, w.partials, w.hist);
   });
   CGB_CUDA(cudaGetLastError());
-  int64_t launches = 1;
+  int64_t launches = 1 + extra;
 
-  const int per_iter = fused ? 2 : 3;
+  const int per_iter = (fused ? 2 : 3) + (int)extra;
   double t_p = 0, t_s = 0, t_u = 0;
   int64_t samples = 0;
   if (persistent) {
@@ -250,7 +253,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
                          (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.eng << 2) ^
-                         ((uint64_t)cfg.l2_window << 4);
+                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)csr_panels(A) << 48);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an

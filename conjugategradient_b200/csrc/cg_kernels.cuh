@@ -39,6 +39,8 @@ struct CsrView {
   const int *sell_long;
   const int64_t *sell_chunk;
   int sell_warp_chunks;
+  // column panels (kEngSell): when set, the row sum handed to the epilogue is panel_acc[row] + (this panel's sum)
+  const double *panel_acc;
 };
 
 // One entry point for the three row engines: CSR with direct loads and L lanes per row (256 threads),
@@ -51,7 +53,7 @@ __device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E 
     spmv_rows_tma<L>(A.n, A.nnz, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
   } else if constexpr (ENG == kEngSell) {
     spmv_rows_sell(A.n, A.sell_slices, A.sell_off, A.sell_cols, A.sell_vals, A.sell_perm, A.sell_nlong, A.sell_long, A.sell_chunk, A.sell_warp_chunks, A.rowptr,
-                   A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
+                   A.cols, A.vals, A.panel_acc, g, e, blockIdx.x, gridDim.x, a0, a1);
   } else {
     spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
   }
@@ -282,9 +284,11 @@ __global__ void CGB_BOUNDS(ENG) residual_kernel(CsrView A, const double *__restr
   }
 }
 
-// y = A x (plain)
+// y = A x (plain).  Also the partial pass of a column panel (A.panel_acc == y: y += A_k x; y is therefore
+// not __restrict__), gated on the CG state when it runs inside the loop.
 template <int L, int ENG>
-__global__ void CGB_BOUNDS(ENG) spmv_kernel(CsrView A, const double *__restrict__ x, double *__restrict__ y) {
+__global__ void CGB_BOUNDS(ENG) spmv_kernel(CsrView A, const double *__restrict__ x, double *y, const CgState *gate) {
+  if (gate && !cg_active(gate)) return;
   double a0 = 0.0, a1 = 0.0;
   GatherPlain g{x};
   EpiStore e{y};

@@ -71,6 +71,8 @@ __global__ void csr_stats_kernel(int64_t n, const int *__restrict__ rowptr, int 
 }
 
 constexpr int kSellDefaultSigma = 32768;
+constexpr int64_t kPanelMinBytes = (int64_t)48 << 20; // gathered vectors up to this size are left in one piece
+constexpr int64_t kPanelBytes = (int64_t)24 << 20;    // target slice of the gathered vector per panel
 
 int csr_prepare(cgb_csr *A) {
   if (A->n == 0) return CGB_OK;
@@ -96,8 +98,26 @@ int csr_prepare(cgb_csr *A) {
     A->auto_sell = A->n >= 4096 && (A->overflow_tiles * 50 > ntiles || (double)A->max_row > 8.0 * mean + 64.0);
     if (const char *env = getenv("CGB_AUTO_SELL")) A->auto_sell = atoi(env) != 0;
   }
-  const bool want_sell = A->format == CGB_FMT_SELL || (A->format == CGB_FMT_AUTO && A->auto_sell);
-  if (want_sell && !A->sell_vals) CGB_TRY(cgb_csr_build_sell(A, kSellDefaultSigma));
+  if (csr_wants_sell(A)) {
+    // Column panels: the gathered vector is read at random columns; when it is larger than what L2 keeps
+    // (the matrix streams through with evict-first, but a B200 L2 half holds ~60 MB), most gathers go to
+    // DRAM at a 32-byte sector per 8-byte value.  Splitting A by column ranges of <= kPanelBytes of the
+    // vector makes each pass's gathers L2 hits, for one extra read+write of the output per extra panel.
+    int P = A->panels_req;
+    if (const char *env = getenv("CGB_SELL_PANELS")) P = atoi(env);
+    if (P <= 0) {
+      const int64_t bytes = 8 * A->n_cols;
+      P = bytes > kPanelMinBytes ? (int)((bytes + kPanelBytes - 1) / kPanelBytes) : 1;
+    }
+    if (!A->panels_ok) P = 1;
+    if (P > 64) P = 64;
+    if (P > 1) {
+      if ((int)A->panels.size() != P) CGB_TRY(csr_build_panels(A, P, A->sell_sigma > 0 ? A->sell_sigma : kSellDefaultSigma));
+    } else {
+      csr_release_panels(A);
+      if (!A->sell_vals) CGB_TRY(cgb_csr_build_sell(A, kSellDefaultSigma));
+    }
+  }
   return CGB_OK;
 }
 
@@ -260,6 +280,7 @@ int cgb_csr_destroy(cgb_csr *A) {
   ScopedDevice sd(A->ctx->device);
   cudaStreamSynchronize(A->ctx->stream);
   workspace_release(A);
+  csr_release_panels(A);
   cudaFree(A->sell_vals);
   cudaFree(A->sell_cols);
   cudaFree(A->sell_off);
@@ -284,15 +305,23 @@ int32_t *cgb_csr_rowptr(cgb_csr *A) { return A ? A->rowptr : nullptr; }
 int cgb_csr_set_format(cgb_csr *A, int format) {
   CGB_REQUIRE(A, "cgb_csr_set_format: NULL matrix");
   CGB_REQUIRE(format == CGB_FMT_AUTO || format == CGB_FMT_CSR || format == CGB_FMT_SELL, "unknown format");
-  if (format == CGB_FMT_SELL && !A->sell_vals) CGB_TRY(cgb_csr_build_sell(A, kSellDefaultSigma));
   if (format != A->format && A->ws.graph) { // cached graphs hold the other engine's kernels
     cudaGraphExecDestroy(A->ws.graph);
     A->ws.graph = nullptr;
   }
   A->format = format;
+  if (format == CGB_FMT_SELL) CGB_TRY(csr_prepare(A)); // builds the SELL copy (or the column panels) now
   return CGB_OK;
 }
 int cgb_csr_get_format(const cgb_csr *A) { return A ? A->format : 0; }
+
+int cgb_csr_set_panels(cgb_csr *A, int panels) {
+  CGB_REQUIRE(A, "cgb_csr_set_panels: NULL matrix");
+  CGB_REQUIRE(panels >= 0 && panels <= 64, "cgb_csr_set_panels: 0 (automatic) .. 64 panels");
+  A->panels_req = panels;
+  return CGB_OK;
+}
+int cgb_csr_get_panels(const cgb_csr *A) { return A ? (int)csr_panels(A) : 0; }
 
 int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
   CGB_REQUIRE(ctx && A && d_x && d_y, "cgb_spmv: NULL argument");
@@ -300,8 +329,10 @@ int cgb_spmv(cgb_ctx *ctx, cgb_csr *A, const double *d_x, double *d_y) {
   ScopedDevice sd(ctx->device);
   CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
+  launch_panel_partials(A, lc, ctx->stream, d_x, d_y, nullptr);
   dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
-    launch_kernel(spmv_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_y);
+    launch_kernel(spmv_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view_final(A, d_y), d_x, d_y,
+                  (const CgState *)nullptr);
   });
   CGB_CUDA(cudaGetLastError());
   return CGB_OK;
@@ -319,8 +350,14 @@ int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b,
   double *out2 = ctx->partials + 2 * kMaxPartials - 2; // tail of the scratch is never a partial slot
   CGB_TRY(csr_prepare(A));
   const SpmvLaunch lc = spmv_launch_cfg(A);
+  double *acc = nullptr;
+  if (csr_panels(A) > 1) { // the pass has no output vector of its own: the workspace's Ap is the accumulator
+    if (!A->ws.Ap) CGB_TRY(workspace_ensure(A, A->n, false, 0));
+    acc = A->ws.Ap;
+    launch_panel_partials(A, lc, ctx->stream, d_x, acc, nullptr);
+  }
   dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
-    launch_kernel(residual_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view(A), d_x, d_b, out2,
+    launch_kernel(residual_kernel<decltype(Lc)::value, decltype(Tc)::value>, lc, ctx->stream, csr_view_final(A, acc), d_x, d_b, out2,
                   ctx->partials, ctx->ticket);
   });
   CGB_CUDA(cudaGetLastError());

@@ -241,6 +241,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   }
   CGB_TRY(cgb_csr_from_device(ctx, n, nnz_loc, vals_loc, cols_loc, rowptr_loc, 1, &d->Aloc));
   CGB_TRY(cgb_csr_from_device(ctx, nh, nnz_halo, vals_halo, cols_halo, rowptr_halo, 1, &d->Ahalo));
+  d->Aloc->panels_ok = d->Ahalo->panels_ok = false; // the distributed loop launches one kernel per block itself
   d->Ahalo->n_cols = H;
 
   // who sends what: receive counts per owner, all-gathered into a matrix

@@ -15,8 +15,14 @@ struct SpmvLaunch {
   int eng; // row engine: kEngVec / kEngTma / kEngSell
 };
 
+inline bool csr_wants_sell(const cgb_csr *A) {
+  return A->format == CGB_FMT_SELL || (A->format == CGB_FMT_AUTO && A->auto_sell);
+}
+// the column panels in use (0: the matrix is streamed as one piece)
+inline size_t csr_panels(const cgb_csr *A) { return csr_wants_sell(A) ? A->panels.size() : 0; }
+
 inline int csr_engine(const cgb_csr *A) {
-  if ((A->format == CGB_FMT_SELL || (A->format == CGB_FMT_AUTO && A->auto_sell)) && A->sell_vals) return kEngSell;
+  if (csr_wants_sell(A) && (A->sell_vals || !A->panels.empty())) return kEngSell;
   return A->use_tma ? kEngTma : kEngVec;
 }
 
@@ -32,7 +38,7 @@ inline SpmvLaunch spmv_launch_cfg(const cgb_csr *A) {
 
 inline CsrView csr_view(const cgb_csr *A) {
   return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals, A->sell_slices, A->sell_off, A->sell_cols, A->sell_vals, A->sell_perm,
-                 A->sell_nlong, A->sell_long, A->sell_chunk, A->sell_warp_chunks};
+                 A->sell_nlong, A->sell_long, A->sell_chunk, A->sell_warp_chunks, nullptr};
 }
 
 // f(std::integral_constant<int, L>, std::integral_constant<int, ENG>)
@@ -61,6 +67,28 @@ inline void launch_kernel(K kernel, const SpmvLaunch &c, cudaStream_t s, Args...
   if (c.smem > 48 * 1024)
     cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
   kernel<<<c.grid, c.block, c.smem, s>>>(args...);
+}
+
+// ---- column panels ---------------------------------------------------------------------------
+// A matrix with panels is A = [A_0 | ... | A_{P-1}] (sell.cu).  An SpMV-shaped pass becomes P launches:
+// panels 0 .. P-2 accumulate their row sums into `acc` (plain spmv_kernel; acc = the pass's own output or
+// a scratch vector), the last panel runs the pass's real kernel on csr_view_final(A, acc), whose engine adds
+// acc[row] to the row sum before the epilogue sees it.  Without panels csr_view_final is csr_view.
+inline CsrView csr_view_final(const cgb_csr *A, const double *acc) {
+  const size_t P = csr_panels(A);
+  if (P == 0) return csr_view(A);
+  CsrView v = csr_view(A->panels[P - 1]);
+  v.panel_acc = P > 1 ? acc : nullptr;
+  return v;
+}
+
+inline void launch_panel_partials(const cgb_csr *A, const SpmvLaunch &c, cudaStream_t s, const double *x, double *acc,
+                                  const CgState *gate) {
+  for (size_t k = 0; k + 1 < csr_panels(A); k++) {
+    CsrView v = csr_view(A->panels[k]);
+    v.panel_acc = k > 0 ? acc : nullptr;
+    launch_kernel(spmv_kernel<1, kEngSell>, c, s, v, x, acc, gate);
+  }
 }
 
 } // namespace cgb

@@ -3,6 +3,8 @@
 #pragma once
 #include "common.cuh"
 
+#include <vector>
+
 namespace cgb {
 
 // Work vectors and scalars of CG::solve (reference allocates them per solve, twice:
@@ -66,11 +68,19 @@ struct cgb_csr {
   int64_t sell_nlong = 0;
   int sell_warp_chunks = 1;
   int64_t *sell_chunk = nullptr; // grid_sell + 1 slice offsets: CTA b streams slices [chunk[b], chunk[b+1]) (equal work)
+  // Column panels (sell.cu: csr_build_panels): A = [A_0 | A_1 | ... ] split by column range so that the slice of
+  // the gathered vector one pass touches fits in L2; every panel is a full SELL matrix over the same rows with
+  // its own row order, processed by consecutive launches that accumulate into the output vector.
+  std::vector<cgb_csr *> panels;
+  int panels_req = 0;    // cgb_csr_set_panels: 0 = automatic (by the size of the gathered vector), 1 = none, P = P panels
+  bool panels_ok = true; // false for the library's internal sub-matrices (panels themselves, multi-GPU blocks)
   cgb::Workspace ws;
 };
 
 namespace cgb {
 int csr_plan(cgb_csr *A);
+int csr_build_panels(cgb_csr *A, int P, int sigma); // sell.cu
+void csr_release_panels(cgb_csr *A);
 int csr_prepare(cgb_csr *A); // before any SpMV-shaped launch: statistics, CGB_FMT_AUTO decision, lazy SELL build
 int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap);
 void workspace_release(cgb_csr *A);

@@ -133,6 +133,7 @@ extern "C" int cgb_csr_build_sell(cgb_csr *A, int sigma) {
   CGB_REQUIRE(sigma >= 1, "cgb_csr_build_sell: sigma must be >= 1");
   if (sigma > 1) sigma = ((sigma + 31) / 32) * 32; // windows are whole slices
   if (A->sell_vals && A->sell_sigma == sigma) return CGB_OK;
+  csr_release_panels(A); // column panels (if any) are rebuilt with the new window by the next csr_prepare
   int long_row = kSellLongRow;
   if (const char *e = getenv("CGB_SELL_LONG")) long_row = atoi(e) > 0 ? atoi(e) : long_row;
   cgb_ctx *ctx = A->ctx;
@@ -240,4 +241,112 @@ extern "C" int cgb_csr_build_sell(cgb_csr *A, int sigma) {
   return CGB_OK;
 }
 
-extern "C" int64_t cgb_csr_sell_padded(const cgb_csr *A) { return A ? A->sell_padded : 0; }
+extern "C" int64_t cgb_csr_sell_padded(const cgb_csr *A) {
+  if (!A) return 0;
+  if (A->panels.empty()) return A->sell_padded;
+  int64_t t = 0;
+  for (const cgb_csr *p : A->panels) t += p->sell_padded;
+  return t;
+}
+
+// ---- column panels ------------------------------------------------------------------------------
+namespace {
+
+// entries of row t with column in [c_lo, c_hi): counted into cnt[t + 1] (cnt[0] = 0 is set by the caller)
+__global__ void panel_count_kernel(int64_t n, const int *__restrict__ rowptr, const int *__restrict__ cols, int c_lo, int c_hi,
+                                   int *__restrict__ cnt) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  int c = 0;
+  for (int j = rowptr[t], e = rowptr[t + 1]; j < e; j++) {
+    const int col = cols[j];
+    c += (col >= c_lo && col < c_hi) ? 1 : 0;
+  }
+  cnt[t + 1] = c;
+}
+
+// copies them in their original order (the reference's left-to-right row sum is kept inside a panel)
+__global__ void panel_fill_kernel(int64_t n, const int *__restrict__ rowptr, const int *__restrict__ cols,
+                                  const double *__restrict__ vals, int c_lo, int c_hi, const int *__restrict__ prow,
+                                  int *__restrict__ pcols, double *__restrict__ pvals) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  int o = prow[t];
+  for (int j = rowptr[t], e = rowptr[t + 1]; j < e; j++) {
+    const int col = cols[j];
+    if (col >= c_lo && col < c_hi) {
+      pcols[o] = col;
+      pvals[o] = vals[j];
+      o++;
+    }
+  }
+}
+
+} // namespace
+
+namespace cgb {
+
+void csr_release_panels(cgb_csr *A) {
+  if (A->panels.empty()) return;
+  for (cgb_csr *p : A->panels) cgb_csr_destroy(p);
+  A->panels.clear();
+  if (A->ws.graph) {
+    cudaGraphExecDestroy(A->ws.graph);
+    A->ws.graph = nullptr;
+  }
+}
+
+// A = [A_0 | ... | A_{P-1}], panel k = columns [n_cols k / P, n_cols (k+1) / P): each a CSR sub-matrix over all
+// rows (owned by its own handle) with its SELL-32-sigma copy; the handles share A's grid so one launch
+// configuration serves every panel.
+int csr_build_panels(cgb_csr *A, int P, int sigma) {
+  csr_release_panels(A);
+  if (P < 2 || A->n == 0) return CGB_OK;
+  cgb_ctx *ctx = A->ctx;
+  ScopedDevice sd(ctx->device);
+  cudaStream_t s = ctx->stream;
+  const int64_t n = A->n;
+  const int tb = 256;
+  const unsigned gb = (unsigned)((n + tb - 1) / tb);
+  for (int k = 0; k < P; k++) {
+    const int c_lo = (int)((A->n_cols * k) / P), c_hi = (int)((A->n_cols * (int64_t)(k + 1)) / P);
+    int *prow = nullptr, *pcols = nullptr;
+    double *pvals = nullptr;
+    Buf g_row, g_cols, g_vals, tmp;
+    CGB_CUDA(cudaMalloc(&prow, sizeof(int) * (size_t)(n + 1) + 64));
+    g_row.p = prow;
+    CGB_CUDA(cudaMemsetAsync(prow, 0, sizeof(int), s));
+    panel_count_kernel<<<gb, tb, 0, s>>>(n, A->rowptr, A->cols, c_lo, c_hi, prow);
+    size_t bytes = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, bytes, prow + 1, prow + 1, (int)n, s);
+    CGB_CUDA(cudaMalloc(&tmp.p, bytes));
+    cub::DeviceScan::InclusiveSum(tmp.p, bytes, prow + 1, prow + 1, (int)n, s);
+    int nnz_k = 0;
+    CGB_CUDA(cudaMemcpyAsync(&nnz_k, prow + n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CGB_CUDA(cudaStreamSynchronize(s));
+    CGB_CUDA(cudaMalloc(&pcols, sizeof(int) * (size_t)nnz_k + 64));
+    g_cols.p = pcols;
+    CGB_CUDA(cudaMalloc(&pvals, sizeof(double) * (size_t)nnz_k + 64));
+    g_vals.p = pvals;
+    panel_fill_kernel<<<gb, tb, 0, s>>>(n, A->rowptr, A->cols, A->vals, c_lo, c_hi, prow, pcols, pvals);
+    CGB_CUDA(cudaGetLastError());
+    CGB_CUDA(cudaStreamSynchronize(s));
+    cgb_csr *S = nullptr;
+    CGB_TRY(cgb_csr_from_device(ctx, n, nnz_k, pvals, pcols, prow, 1, &S));
+    g_row.p = g_cols.p = g_vals.p = nullptr; // owned by the panel's handle now
+    S->n_cols = A->n_cols;
+    S->panels_ok = false;
+    S->format = CGB_FMT_SELL;
+    S->stats_done = true; // never planned on its own: always streamed through the SELL engine
+    S->grid_sell = A->grid_sell;
+    A->panels.push_back(S);
+    CGB_TRY(cgb_csr_build_sell(S, sigma));
+  }
+  if (A->ws.graph) {
+    cudaGraphExecDestroy(A->ws.graph);
+    A->ws.graph = nullptr;
+  }
+  return CGB_OK;
+}
+
+} // namespace cgb

@@ -157,8 +157,9 @@ __device__ __forceinline__ void spmv_rows_sell(int64_t n, int64_t slices, const 
                                                const int *__restrict__ perm, int64_t nlong,
                                                const int *__restrict__ long_rows, const int64_t *__restrict__ chunk,
                                                int warp_chunks, const int *__restrict__ rowptr,
-                                               const int *__restrict__ ccols, const double *__restrict__ cvals, const G &g,
-                                               const E &e, int bid, int nb, double &a0, double &a1) {
+                                               const int *__restrict__ ccols, const double *__restrict__ cvals,
+                                               const double *acc, const G &g, const E &e, int bid, int nb, double &a0,
+                                               double &a1) {
   uint64_t pol;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
   const int lane = threadIdx.x & 31;
@@ -194,7 +195,10 @@ __device__ __forceinline__ void spmv_rows_sell(int64_t n, int64_t slices, const 
     const int64_t slot = s * 32 + lane;
     if (slot < n) {
       const int64_t row = perm ? (int64_t)perm[slot] : slot;
-      if (row >= 0) e.row(row, sum, a0, a1); // negative: a long row, handled below
+      if (row >= 0) { // negative: a long row, handled below
+        if (acc) sum += acc[row]; // column panels: what the earlier panels summed for this row
+        e.row(row, sum, a0, a1);
+      }
     }
   }
   // long rows: a warp per row over the CSR arrays (coalesced), two steps in flight, shuffle reduction
@@ -211,7 +215,10 @@ __device__ __forceinline__ void spmv_rows_sell(int64_t n, int64_t slices, const 
     }
     if (j < en) s0 = fma(ld_stream_f64_ef(cvals + j, pol), g(ld_stream_s32_ef(ccols + j, pol)), s0);
     double sum = warp_sum(s0 + s1);
-    if (lane == 0) e.row(row, sum, a0, a1);
+    if (lane == 0) {
+      if (acc) sum += acc[row];
+      e.row(row, sum, a0, a1);
+    }
   }
 }
 

@@ -169,6 +169,13 @@ class Matrix:
             L.check(self.ctx.lib.cgb_csr_build_sell(self.h, sigma))
         L.check(self.ctx.lib.cgb_csr_set_format(self.h, fmt))
 
+    def set_panels(self, panels: int):
+        """Column panels of the SELL engine: 0 automatic, 1 none, P exactly P (include/cgb200.h)."""
+        L.check(self.ctx.lib.cgb_csr_set_panels(self.h, panels))
+
+    def panels(self) -> int:
+        return int(self.ctx.lib.cgb_csr_get_panels(self.h))
+
     def sell_padded(self) -> int:
         return int(self.ctx.lib.cgb_csr_sell_padded(self.h))
 

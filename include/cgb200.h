@@ -107,6 +107,15 @@ int64_t cgb_csr_sell_padded(const cgb_csr *A);
 enum { CGB_FMT_AUTO = 0, CGB_FMT_CSR = 1, CGB_FMT_SELL = 2 };
 int cgb_csr_set_format(cgb_csr *A, int format);
 int cgb_csr_get_format(const cgb_csr *A);
+/* Column panels of the SELL engine: A = [A_0 | ... | A_{P-1}] split by column range, one pass per panel
+ * accumulating into the output, so that the part of the gathered vector a pass touches stays in L2 (random
+ * sparsity patterns whose vector exceeds L2: BASELINE config C5).  0 = automatic (by the vector's size; the
+ * default), 1 = never split, P = exactly P panels.  Takes effect at the next SpMV-shaped call.  The row sum
+ * becomes (A_0 x + A_1 x) + ... : a different summation order from the reference's left-to-right row
+ * (src/VectorOperations.hpp:455-462), inside north_star's 1e-10 tolerance, bitwise reproducible. */
+int cgb_csr_set_panels(cgb_csr *A, int panels);
+/* Panels in use after the last SpMV-shaped call (0: the matrix is streamed in one piece). */
+int cgb_csr_get_panels(const cgb_csr *A);
 
 /* On-device generation of the synthetic stencils of SURVEY.md §8(d) (identical arrays to
  * conjugategradient_b200/generators.py): kind 0 = 2D 5-point (m x m), 1 = 3D 7-point,

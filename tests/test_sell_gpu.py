@@ -121,3 +121,69 @@ def test_random_spd_generator_properties(ctx, port):
     st = cg.solve(tol)
     assert abs(st["iterations"] - o["iterations"]) <= max(1, round(0.05 * o["iterations"]))
     assert rel_err(cg.extract(), o["x"]) <= 1e-10
+
+
+# ---- column panels: A = [A_0 | ... | A_{P-1}], one pass per panel accumulating into the output ------------
+@pytest.mark.parametrize("panels", [2, 3, 7])
+@pytest.mark.parametrize("name", ["p2d_33", "rspd_20000", "rspd_777", "diag_1"])
+def test_sell_panels_spmv_and_accuracy(ctx, port, name, panels):
+    v, c, r = MATS[name]()
+    n = r.size - 1
+    rng = np.random.default_rng(5)
+    z, b = rng.standard_normal(n), rng.standard_normal(n)
+    A = S.Matrix(ctx, v, c, r)
+    A.set_panels(panels)
+    A.set_format(L.FMT_SELL, 1024)
+    assert A.panels() == panels
+    ops = S.VectorOperations(ctx)
+    ops.setVectorSize(n)
+    Z, O = S.Vector(ctx, z), S.Vector(ctx, n=n)
+    ops.spmv(A, Z, O)
+    exp = port.spmv(v, c, r, z)
+    absrow = port.spmv(np.abs(v), c, r, np.abs(z))
+    # the row sum is (panel 0) + (panel 1) + ...: a different association, still a few ulp of the absolute sum
+    assert np.all(np.abs(O.download() - exp) <= 4e-16 * absrow * (4 + panels))
+    first = O.download().copy()
+    ops.spmv(A, Z, O)
+    assert np.array_equal(first, O.download())                        # bitwise reproducible
+    cg = S.CG(ctx)
+    cg.setMatrix(A)
+    cg.setTarget(b)
+    cg.setInital(z)
+    acc, rr, xx = port.accuracy(v, c, r, z, b)
+    grr, gxx = cg.residual()
+    assert abs(grr - rr) <= 1e-13 * rr and abs(gxx - xx) <= 1e-13 * xx
+    # back to one piece on the same handle
+    A.set_panels(1)
+    ops.spmv(A, Z, O)
+    assert A.panels() == 0
+    assert np.all(np.abs(O.download() - exp) <= 4e-16 * absrow * 4)
+
+
+@pytest.mark.parametrize("panels", [2, 4])
+@pytest.mark.parametrize("name,rel", [("p3d7_30", 1e-8), ("rspd_50000", 1e-10)])
+def test_sell_panels_solve_vs_oracle(ctx, port, name, rel, panels):
+    gen = {"p3d7_30": lambda: G.poisson3d_7pt(30), "rspd_50000": lambda: G.random_spd_powerlaw(50000, seed=21)}[name]
+    v, c, r = gen()
+    n = r.size - 1
+    b = G.default_rhs(n)
+    tol = rel * np.linalg.norm(b)
+    o = port.cg_solve(v, c, r, b, tol)
+    A = S.Matrix(ctx, v, c, r)
+    A.set_panels(panels)
+    A.set_format(L.FMT_SELL)
+    cg = S.CG(ctx, record_history=1)
+    cg.setMatrix(A)
+    cg.setTarget(b)
+    st = cg.solve(tol)
+    assert A.panels() == panels and st["format"] == L.FMT_SELL and st["converged"] == 1
+    assert st["kernel_launches"] >= st["iterations"] * (3 + panels - 1)
+    slack = 0.05 if name.startswith("rspd") else 0.02
+    assert abs(st["iterations"] - o["iterations"]) <= max(1, round(slack * o["iterations"]))
+    x1 = cg.extract()
+    assert rel_err(x1, o["x"]) <= 1e-10
+    rr, _ = cg.residual()
+    assert np.sqrt(rr) <= 10 * tol
+    cg.x = None
+    cg.solve(tol)
+    assert np.array_equal(cg.extract(), x1)                           # deterministic run to run

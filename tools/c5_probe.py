@@ -21,15 +21,19 @@ def main():
     b = np.arange(1, n + 1, dtype=np.float64)
     tol = 1e-8 * float(np.sqrt(n * (n + 1) * (2 * n + 1) / 6.0))
     B_iter = 12 * nnz + 4 * (n + 1) + 88 * n
-    cfgs = os.environ.get("C5_CONFIGS", "csr:0,sell:1,sell:1024,sell:4096,sell:32768,sell:262144")
-    for fmt, sigma in [((L.FMT_SELL if a == "sell" else L.FMT_CSR), int(b_)) for a, b_ in (c.split(":") for c in cfgs.split(","))]:
+    # format:sigma[:panels]   (panels: 0 automatic, 1 none, P column panels)
+    cfgs = os.environ.get("C5_CONFIGS", "csr:0,sell:32768:1,sell:32768:2,sell:32768:3,sell:32768:4,sell:32768:6,sell:32768:8")
+    for cfg in cfgs.split(","):
+        f = cfg.split(":")
+        fmt, sigma, panels = (L.FMT_SELL if f[0] == "sell" else L.FMT_CSR), int(f[1]), int(f[2]) if len(f) > 2 else 1
         A.set_format(L.FMT_CSR)
         if fmt == L.FMT_SELL:
             t0 = time.time()
+            A.set_panels(panels)
             L.check(ctx.lib.cgb_csr_build_sell(A.h, sigma))
+            A.set_format(L.FMT_SELL)
             ctx.sync()
             tb = time.time() - t0
-            A.set_format(L.FMT_SELL)
         for fused in (0,):
             cg = S.CG(ctx, fuse_p_update=fused, time_kernels=1)
             cg.setMatrix(A)
@@ -40,7 +44,7 @@ def main():
             sec = st["solve_ms"] / 1e3
             it = st["iterations"]
             rr, xx = cg.residual()
-            extra = f" sell_padded={A.sell_padded() / nnz:.3f}x build={tb:.2f}s sigma={sigma}" if fmt == L.FMT_SELL else ""
+            extra = f" sell_padded={A.sell_padded() / nnz:.3f}x build={tb:.2f}s sigma={sigma} panels={A.panels()}" if fmt == L.FMT_SELL else ""
             print(f"fmt={'SELL' if fmt == L.FMT_SELL else 'CSR '} fused={fused} it={it} {it / sec:8.1f} it/s {it * B_iter / sec / 1e9:7.1f} GB/s(B_iter) "
                   f"spmv {st['spmv_ms']:.4f} ms true_rel_res={np.sqrt(rr) / (tol / 1e-8):.2e}{extra}", flush=True)
 

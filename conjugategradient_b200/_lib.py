@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcgb200.so")
+LIB_PATH = os.environ.get("CGB_LIB_PATH") or os.path.join(_HERE, "libcgb200.so")  # override: A/B builds of the same library
 
 c_i64 = C.c_int64
 c_dp = C.POINTER(C.c_double)

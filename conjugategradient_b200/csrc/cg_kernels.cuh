@@ -32,13 +32,13 @@ struct CsrView {
   // SELL-32-sigma shadow copy (engine kEngSell only)
   int64_t sell_slices;
   const int64_t *sell_off;
+  const int *sell_width;
   const int *sell_cols;
   const double *sell_vals;
   const int *sell_perm;
   int64_t sell_nlong;
   const int *sell_long;
   const int64_t *sell_chunk;
-  int sell_warp_chunks;
   // column panels (kEngSell): when set, the row sum handed to the epilogue is panel_acc[row] + (this panel's sum)
   const double *panel_acc;
 };
@@ -52,13 +52,13 @@ __device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E 
     extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
     spmv_rows_tma<L>(A.n, A.nnz, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
   } else if constexpr (ENG == kEngSell) {
-    spmv_rows_sell(A.n, A.sell_slices, A.sell_off, A.sell_cols, A.sell_vals, A.sell_perm, A.sell_nlong, A.sell_long, A.sell_chunk, A.sell_warp_chunks, A.rowptr,
-                   A.cols, A.vals, A.panel_acc, g, e, blockIdx.x, gridDim.x, a0, a1);
+    spmv_rows_sell(A.n, A.sell_slices, A.sell_off, A.sell_width, A.sell_cols, A.sell_vals, A.sell_perm, A.sell_nlong, A.sell_long,
+                   A.sell_chunk, A.rowptr, A.cols, A.vals, A.panel_acc, g, e, blockIdx.x, gridDim.x, a0, a1);
   } else {
     spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
   }
 }
-#define CGB_BOUNDS(ENG) __launch_bounds__((ENG) == kEngTma ? kTmaThreads : kBlock)
+#define CGB_BOUNDS(ENG) __launch_bounds__((ENG) == kEngTma ? kTmaThreads : kBlock, (ENG) == kEngSell ? kSellMinCtas : 1)
 
 __device__ __forceinline__ bool cg_active(const CgState *st) {
   // reference: do { ... } while (counter++ < N && !*is_done)   (src/CG.hpp:436)

@@ -18,7 +18,13 @@ int csr_plan(cgb_csr *A) {
   A->lanes = lanes;
   const int sms = A->ctx->sm_count;
   A->grid_spmv = sms * 8;
-  A->grid_sell = sms * 8;
+  // SELL engine: every warp owns one cost-balanced range of slices; many more CTAs than fit at once (24 per SM,
+  // measured on C5: 8 -> 1.17 ms, 16 -> 1.11, 24 -> 1.09), so the hardware scheduler evens out what the static cost
+  // model misses.  Never more CTAs than reduction partials.
+  int sell_per_sm = 24;
+  if (const char *e = getenv("CGB_SELL_CTAS")) sell_per_sm = atoi(e) > 0 ? atoi(e) : sell_per_sm;
+  A->grid_sell = sms * sell_per_sm;
+  if (A->grid_sell > kMaxPartials) A->grid_sell = kMaxPartials;
   if ((A->n + 255) / 256 < A->grid_sell) A->grid_sell = (int)((A->n + 255) / 256 > 0 ? (A->n + 255) / 256 : 1);
   // streaming vector kernels: exactly one resident wave (grid-stride loops), so no partial second wave
   // leaves SMs idle at the tail; CGB_VEC_CTAS caps the CTAs per SM for A/B measurements
@@ -72,7 +78,7 @@ __global__ void csr_stats_kernel(int64_t n, const int *__restrict__ rowptr, int 
 
 constexpr int kSellDefaultSigma = 32768;
 constexpr int64_t kPanelMinBytes = (int64_t)48 << 20; // gathered vectors up to this size are left in one piece
-constexpr int64_t kPanelBytes = (int64_t)24 << 20;    // target slice of the gathered vector per panel
+constexpr int64_t kPanelBytes = (int64_t)40 << 20;    // target slice of the gathered vector per panel (C5: 2 x 40 MB wins)
 
 int csr_prepare(cgb_csr *A) {
   if (A->n == 0) return CGB_OK;
@@ -284,6 +290,7 @@ int cgb_csr_destroy(cgb_csr *A) {
   cudaFree(A->sell_vals);
   cudaFree(A->sell_cols);
   cudaFree(A->sell_off);
+  cudaFree(A->sell_width);
   cudaFree(A->sell_perm);
   cudaFree(A->sell_long);
   cudaFree(A->sell_chunk);

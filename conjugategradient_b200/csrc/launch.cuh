@@ -37,8 +37,8 @@ inline SpmvLaunch spmv_launch_cfg(const cgb_csr *A) {
 }
 
 inline CsrView csr_view(const cgb_csr *A) {
-  return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals, A->sell_slices, A->sell_off, A->sell_cols, A->sell_vals, A->sell_perm,
-                 A->sell_nlong, A->sell_long, A->sell_chunk, A->sell_warp_chunks, nullptr};
+  return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals, A->sell_slices, A->sell_off, A->sell_width, A->sell_cols, A->sell_vals, A->sell_perm,
+                 A->sell_nlong, A->sell_long, A->sell_chunk, nullptr};
 }
 
 // f(std::integral_constant<int, L>, std::integral_constant<int, ENG>)

@@ -62,12 +62,12 @@ struct cgb_csr {
   int64_t sell_padded = 0;
   double *sell_vals = nullptr;
   int32_t *sell_cols = nullptr;
+  int32_t *sell_width = nullptr; // column-major steps per slice (sell_slices)
   int64_t *sell_off = nullptr;  // slice offsets (in entries), sell_slices + 1
   int32_t *sell_perm = nullptr; // slot -> row, ~row for rows served from the long-row list (NULL: identity, no long rows)
   int32_t *sell_long = nullptr; // rows longer than kSellLongRow: processed a warp per row from the CSR arrays
   int64_t sell_nlong = 0;
-  int sell_warp_chunks = 1;
-  int64_t *sell_chunk = nullptr; // grid_sell + 1 slice offsets: CTA b streams slices [chunk[b], chunk[b+1]) (equal work)
+  int64_t *sell_chunk = nullptr; // grid_sell * 8 + 1 slice offsets: warp w streams slices [chunk[w], chunk[w+1]) (equal cost)
   // Column panels (sell.cu: csr_build_panels): A = [A_0 | A_1 | ... ] split by column range so that the slice of
   // the gathered vector one pass touches fits in L2; every panel is a full SELL matrix over the same rows with
   // its own row order, processed by consecutive launches that accumulate into the output vector.

@@ -61,7 +61,7 @@ struct IsLongRow {
 
 // a warp per slice: width = max row length over its slots
 __global__ void sell_width_kernel(int64_t n, int64_t slices, const int *__restrict__ rowptr, const int *__restrict__ perm,
-                                  int long_row, int64_t *__restrict__ entries) {
+                                  int long_row, int64_t *__restrict__ entries, int *__restrict__ widths) {
   const int lane = threadIdx.x & 31;
   const int64_t s = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (s >= slices) return;
@@ -73,7 +73,10 @@ __global__ void sell_width_kernel(int64_t n, int64_t slices, const int *__restri
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) len = max(len, __shfl_xor_sync(0xffffffffu, len, o));
-  if (lane == 0) entries[s] = (int64_t)len * 32;
+  if (lane == 0) {
+    entries[s] = (int64_t)len * 32;
+    widths[s] = len;
+  }
 }
 
 __global__ void sell_fill_kernel(int64_t n, int64_t slices, const int *__restrict__ rowptr, const int *__restrict__ cols,
@@ -105,17 +108,19 @@ __global__ void sell_fill_kernel(int64_t n, int64_t slices, const int *__restric
   }
 }
 
-// chunk[b] = first slice of CTA b: contiguous slice ranges of (nearly) equal stored entries, so that the
-// static assignment is balanced by WORK whatever the row-length distribution and sorting window are
+// chunk[b] = first slice of warp b: contiguous slice ranges of (nearly) equal COST, so that the static assignment
+// is balanced whatever the row-length distribution and sorting window are.  cost(slice) = its column-major steps
+// + kSliceCost for the per-slice work (slot -> row lookup, epilogue), which dominates when rows are short.
+constexpr int64_t kSliceCost = 2;
 __global__ void sell_chunk_kernel(int64_t slices, const int64_t *__restrict__ off, int nb, int64_t *__restrict__ chunk) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nb) return;
-  const int64_t total = off[slices];
+  const int64_t total = (off[slices] >> 5) + kSliceCost * slices;
   const int64_t target = (int64_t)(((__int128)total * b) / nb);
-  int64_t lo = 0, hi = slices; // first slice whose offset is >= target
+  int64_t lo = 0, hi = slices; // first slice whose cost prefix is >= target
   while (lo < hi) {
     const int64_t mid = (lo + hi) >> 1;
-    if (off[mid] < target) lo = mid + 1; else hi = mid;
+    if ((off[mid] >> 5) + kSliceCost * mid < target) lo = mid + 1; else hi = mid;
   }
   chunk[b] = b == nb ? slices : lo;
 }
@@ -143,6 +148,8 @@ extern "C" int cgb_csr_build_sell(cgb_csr *A, int sigma) {
   cudaFree(A->sell_vals);
   cudaFree(A->sell_cols);
   cudaFree(A->sell_off);
+  cudaFree(A->sell_width);
+  A->sell_width = nullptr;
   cudaFree(A->sell_perm);
   cudaFree(A->sell_long);
   cudaFree(A->sell_chunk);
@@ -208,7 +215,8 @@ extern "C" int cgb_csr_build_sell(cgb_csr *A, int sigma) {
     sell_mark_long_kernel<<<blocks(n), tb, 0, s>>>(n, A->rowptr, long_row, A->sell_perm);
   }
   CGB_CUDA(cudaMalloc(&A->sell_off, sizeof(int64_t) * (size_t)(slices + 1)));
-  sell_width_kernel<<<blocks(slices * 32), tb, 0, s>>>(n, slices, A->rowptr, A->sell_perm, long_row, A->sell_off);
+  CGB_CUDA(cudaMalloc(&A->sell_width, sizeof(int) * (size_t)slices + 256));
+  sell_width_kernel<<<blocks(slices * 32), tb, 0, s>>>(n, slices, A->rowptr, A->sell_perm, long_row, A->sell_off, A->sell_width);
   CGB_CUDA(cudaMemsetAsync(A->sell_off + slices, 0, sizeof(int64_t), s));
   {
     Buf tmp;
@@ -227,10 +235,8 @@ extern "C" int cgb_csr_build_sell(cgb_csr *A, int sigma) {
                                                       A->sell_cols, A->sell_vals);
   CGB_CUDA(cudaGetLastError());
   CGB_CUDA(cudaStreamSynchronize(s));
-  // one contiguous, work-balanced slice range per WARP (kBlock / 32 warps per CTA); CGB_SELL_BAL=cta: per CTA
-  const char *bal = getenv("CGB_SELL_BAL");
-  A->sell_warp_chunks = !(bal && !strcmp(bal, "cta"));
-  const int units = A->grid_sell * (A->sell_warp_chunks ? kBlock / 32 : 1);
+  // one contiguous, cost-balanced slice range per WARP (kBlock / 32 warps per CTA)
+  const int units = A->grid_sell * (kBlock / 32);
   CGB_CUDA(cudaMalloc(&A->sell_chunk, sizeof(int64_t) * (size_t)(units + 1)));
   sell_chunk_kernel<<<blocks(units + 1), tb, 0, s>>>(slices, A->sell_off, units, A->sell_chunk);
   CGB_CUDA(cudaGetLastError());

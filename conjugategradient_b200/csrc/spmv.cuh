@@ -151,53 +151,113 @@ __device__ __forceinline__ int ld_stream_s32_ef(const int *p, uint64_t pol) {
   return v;
 }
 
+#ifndef CGB_SELL_U
+#define CGB_SELL_U 4
+#endif
+#ifndef CGB_SELL_MINB
+#define CGB_SELL_MINB 4
+#endif
+constexpr int kSellUnroll = CGB_SELL_U;  // column-major steps per load group
+constexpr int kSellMinCtas = CGB_SELL_MINB; // resident CTAs per SM the register budget is sized for
+
+// The warp streams its contiguous range of slices as ONE sequence of column-major steps: the loads of a group of
+// kSellUnroll steps are issued while the previous group's gathers come back, whatever the slice boundaries are,
+// so narrow slices (short rows, or a column panel of a longer row) cost no extra memory round trip.  Slice
+// bookkeeping rides along: widths arrive 32 slices at a time (lane i holds slice sb + i), the slot -> row map is
+// read two slices ahead and the panel accumulator one slice ahead of its use.
 template <class G, class E>
 __device__ __forceinline__ void spmv_rows_sell(int64_t n, int64_t slices, const int64_t *__restrict__ off,
-                                               const int *__restrict__ cols, const double *__restrict__ vals,
-                                               const int *__restrict__ perm, int64_t nlong,
+                                               const int *__restrict__ width, const int *__restrict__ cols,
+                                               const double *__restrict__ vals, const int *__restrict__ perm, int64_t nlong,
                                                const int *__restrict__ long_rows, const int64_t *__restrict__ chunk,
-                                               int warp_chunks, const int *__restrict__ rowptr,
-                                               const int *__restrict__ ccols, const double *__restrict__ cvals,
-                                               const double *acc, const G &g, const E &e, int bid, int nb, double &a0,
-                                               double &a1) {
+                                               const int *__restrict__ rowptr, const int *__restrict__ ccols,
+                                               const double *__restrict__ cvals, const double *acc, const G &g, const E &e,
+                                               int bid, int nb, double &a0, double &a1) {
+  constexpr int U = kSellUnroll;
   uint64_t pol;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
   const int lane = threadIdx.x & 31;
   const int64_t warp_id = (int64_t)bid * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)nb * (blockDim.x >> 5);
-  // every warp (or CTA, whose warps then take slices round-robin) streams its own contiguous range of
-  // slices holding an equal share of the stored entries: static, deterministic, balanced by work
-  const int wpb = blockDim.x >> 5;
-  const int64_t unit = warp_chunks ? warp_id : (int64_t)bid;
-  const int64_t s_end = chunk[unit + 1];
-  const int64_t s_step = warp_chunks ? 1 : wpb;
-  for (int64_t s = chunk[unit] + (warp_chunks ? 0 : (threadIdx.x >> 5)); s < s_end; s += s_step) {
-    const int64_t o0 = off[s], o1 = off[s + 1];
+  // every warp streams its own contiguous range of slices of (nearly) equal cost: static, deterministic
+  int64_t s = chunk[warp_id];
+  const int64_t s_end = chunk[warp_id + 1];
+  if (s < s_end) {
+    auto slot_row = [&](int64_t sl) -> int { // < 0: no row behind this slot (tail of the last slice, or a long row)
+      const int64_t slot = sl * 32 + lane;
+      return slot < n ? (perm ? perm[slot] : (int)slot) : -1;
+    };
+    int row = slot_row(s);
+    int row_next = s + 1 < s_end ? slot_row(s + 1) : -1;
+    double accv = (acc && row >= 0) ? acc[row] : 0.0; // column panels: what the earlier panels summed for this row
+    int64_t sb = s;
+    int myw = sb + lane < s_end ? width[sb + lane] : 0;
+    int q = 0;
+    int left = __shfl_sync(0xffffffffu, myw, 0);
     double sum = 0.0;
-    int64_t j = o0 + lane;
-    for (; j + 96 < o1; j += 128) { // four column-major steps in flight
-      const int c0 = ld_stream_s32_ef(cols + j, pol), c1 = ld_stream_s32_ef(cols + j + 32, pol);
-      const int c2 = ld_stream_s32_ef(cols + j + 64, pol), c3 = ld_stream_s32_ef(cols + j + 96, pol);
-      const double v0 = ld_stream_f64_ef(vals + j, pol), v1 = ld_stream_f64_ef(vals + j + 32, pol);
-      const double v2 = ld_stream_f64_ef(vals + j + 64, pol), v3 = ld_stream_f64_ef(vals + j + 96, pol);
-      const double x0 = c0 >= 0 ? g(c0) : 0.0, x1 = c1 >= 0 ? g(c1) : 0.0;
-      const double x2 = c2 >= 0 ? g(c2) : 0.0, x3 = c3 >= 0 ? g(c3) : 0.0;
-      if (c0 >= 0) sum = fma(v0, x0, sum);
-      if (c1 >= 0) sum = fma(v1, x1, sum);
-      if (c2 >= 0) sum = fma(v2, x2, sum);
-      if (c3 >= 0) sum = fma(v3, x3, sum);
+    auto finish = [&]() { // slice s is complete (warp-uniform)
+      if (row >= 0) e.row(row, sum + accv, a0, a1);
+      sum = 0.0;
+      s++;
+      if (++q == 32) {
+        sb += 32;
+        myw = sb + lane < s_end ? width[sb + lane] : 0;
+        q = 0;
+      }
+      left = __shfl_sync(0xffffffffu, myw, q);
+      row = row_next;
+      accv = (acc && row >= 0) ? acc[row] : 0.0;
+      row_next = s + 1 < s_end ? slot_row(s + 1) : -1;
+    };
+    while (s < s_end && left == 0) finish(); // leading empty slices
+    const int64_t j0 = off[chunk[warp_id]];
+    const int64_t T = (off[s_end] - j0) >> 5; // column-major steps of this range
+    const int *cp = cols + j0 + lane;
+    const double *vp = vals + j0 + lane;
+    int c[U];
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (u < T) {
+        c[u] = ld_stream_s32_ef(cp + 32 * u, pol);
+        v[u] = ld_stream_f64_ef(vp + 32 * u, pol);
+      } else {
+        c[u] = -1;
+        v[u] = 0.0;
+      }
     }
-    for (; j < o1; j += 32) {
-      const int c = ld_stream_s32_ef(cols + j, pol);
-      const double v = ld_stream_f64_ef(vals + j, pol);
-      if (c >= 0) sum = fma(v, g(c), sum);
-    }
-    const int64_t slot = s * 32 + lane;
-    if (slot < n) {
-      const int64_t row = perm ? (int64_t)perm[slot] : slot;
-      if (row >= 0) { // negative: a long row, handled below
-        if (acc) sum += acc[row]; // column panels: what the earlier panels summed for this row
-        e.row(row, sum, a0, a1);
+    for (int64_t t = 0; t < T; t += U) {
+      double x[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) x[u] = c[u] >= 0 ? g(c[u]) : 0.0; // padding carries column -1: never multiplied
+      int cn[U];
+      double vn[U];
+      cp += 32 * U;
+      vp += 32 * U;
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        if (t + U + u < T) {
+          cn[u] = ld_stream_s32_ef(cp + 32 * u, pol);
+          vn[u] = ld_stream_f64_ef(vp + 32 * u, pol);
+        } else {
+          cn[u] = -1;
+          vn[u] = 0.0;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        if (t + u < T) { // warp-uniform
+          if (c[u] >= 0) sum = fma(v[u], x[u], sum);
+          if (--left == 0) {
+            finish();
+            while (s < s_end && left == 0) finish();
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        c[u] = cn[u];
+        v[u] = vn[u];
       }
     }
   }

@@ -19,6 +19,8 @@ c_vp = C.c_void_p
 
 CGB_OK, CGB_ERR_INVALID, CGB_ERR_CUDA, CGB_ERR_NCCL, CGB_ERR_STATE, CGB_ERR_IO = range(6)
 FMT_AUTO, FMT_CSR, FMT_SELL = 0, 1, 2
+COO_MIRROR, COO_SUM_DUPLICATES, COO_COMPACT_ROWS, COO_ONE_BASED = 1, 2, 4, 8
+COO_REFERENCE_DIALECT = COO_MIRROR | COO_COMPACT_ROWS | COO_ONE_BASED
 LOOP_AUTO, LOOP_GRAPH, LOOP_PERSISTENT, LOOP_STEPWISE = 0, 1, 2, 3
 NCCL_ID_BYTES = 128
 
@@ -82,6 +84,9 @@ SIGNATURES = {
     "cgb_csr_set_format": (C.c_int, [c_vp, C.c_int]),
     "cgb_csr_get_format": (C.c_int, [c_vp]),
     "cgb_csr_set_panels": (C.c_int, [c_vp, C.c_int]),
+    "cgb_csr_from_triplets": (C.c_int, [c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, C.c_int, C.POINTER(c_vp)]),
+    "cgb_csr_from_triplets_device": (C.c_int, [c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, C.c_int, C.POINTER(c_vp)]),
+    "cgb_csr_from_mm_file": (C.c_int, [c_vp, C.c_char_p, C.POINTER(c_vp)]),
     "cgb_csr_get_panels": (C.c_int, [c_vp]),
     "cgb_gen_stencil": (C.c_int, [c_vp, C.c_int, c_i64, c_i64, c_i64, c_i64, C.POINTER(c_vp)]),
     "cgb_gen_random_spd": (C.c_int, [c_vp, c_i64, C.c_uint64, C.c_int, C.c_int, C.c_double, c_i64, c_i64, C.POINTER(c_vp)]),

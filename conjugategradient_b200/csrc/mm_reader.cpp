@@ -1,7 +1,9 @@
 // mm_reader.cpp — Matrix Market coordinate-real reader, dialect-compatible with the reference's
 // read_file (reference test/mm_reader.cpp:154-171 and :45-107) but built differently: the file is
-// read in one block, numbers are parsed with from_chars, and the CSR is assembled with a counting
-// sort over rows (O(nnz)) plus a per-row column sort, instead of a comparison sort over tuples.
+// memory-mapped and its body parsed with from_chars on all host cores (one line-aligned chunk per
+// thread), and the host CSR is assembled with a counting sort over rows (O(nnz)) plus a per-row
+// column sort, instead of a comparison sort over tuples.  cgb_csr_from_mm_file (coo.cu) feeds the
+// same triplets to the GPU assembly instead.
 //
 // Dialect kept on purpose:
 //   * the banner line is consumed and ignored (:160, parse_header result unused);
@@ -15,6 +17,11 @@
 #include "../../include/cgb200.h"
 
 #include <algorithm>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <thread>
+#include <unistd.h>
 #include <charconv>
 #include <cstdio>
 #include <cstdlib>
@@ -59,48 +66,134 @@ inline bool parse_double(const char *&p, const char *end, double &out) {
   return true;
 }
 
+// One chunk of the body, line-aligned: every non-blank line must be exactly "i j v".  Returns false when a line
+// does not fit that shape (the caller then re-parses the whole body as a token stream, which is the reference's
+// own reading loop, test/mm_reader.cpp:62-66).
+bool parse_lines(const char *p, const char *end, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv) {
+  const size_t guess = (size_t)(end - p) / 12 + 16;
+  ri.reserve(guess);
+  ci.reserve(guess);
+  vv.reserve(guess);
+  long a, b;
+  double v;
+  while (p < end) {
+    while (p < end && (*p == ' ' || *p == '\t' || *p == '\r')) p++;
+    if (p < end && *p == '\n') { // blank line
+      p++;
+      continue;
+    }
+    if (p >= end) break;
+    if (!parse_int(p, end, a) || !parse_int(p, end, b) || !parse_double(p, end, v)) return false;
+    while (p < end && (*p == ' ' || *p == '\t' || *p == '\r')) p++;
+    if (p < end && *p != '\n') return false; // a fourth token on the line
+    ri.push_back((int32_t)a);
+    ci.push_back((int32_t)b);
+    vv.push_back(v);
+  }
+  return true;
+}
+
 } // namespace
+
+namespace cgb {
+
+// Body of a Matrix Market file in the reference dialect -> 1-based triplets, in file order.  The file is mapped,
+// cut at line ends into one chunk per host thread and parsed with from_chars; files whose lines are not plain
+// "i j v" fall back to the serial token stream.
+int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv) {
+  ri.clear();
+  ci.clear();
+  vv.clear();
+  const int fd = ::open(path, O_RDONLY);
+  if (fd < 0) return fail(CGB_ERR_IO, "cgb_mm_read: cannot open '%s'", path);
+  struct stat st;
+  if (::fstat(fd, &st) != 0 || !S_ISREG(st.st_mode)) {
+    ::close(fd);
+    return fail(CGB_ERR_IO, "cgb_mm_read: cannot stat '%s'", path);
+  }
+  const size_t sz = (size_t)st.st_size;
+  if (sz == 0) {
+    ::close(fd);
+    return CGB_OK;
+  }
+  void *map = ::mmap(nullptr, sz, PROT_READ, MAP_PRIVATE, fd, 0);
+  ::close(fd);
+  if (map == MAP_FAILED) return fail(CGB_ERR_IO, "cgb_mm_read: cannot map '%s'", path);
+  ::madvise(map, sz, MADV_SEQUENTIAL);
+  const char *p = (const char *)map, *end = p + sz;
+  p = skip_line(p, end);                              // banner (test/mm_reader.cpp:160; result unused there too)
+  p = skip_line(p, end);                              // unconditional discard (:163-164)
+  while (p < end && *p == '%') p = skip_line(p, end); // comments (:146-152)
+  p = skip_line(p, end);                              // size line (:47-52, numbers unused)
+
+  unsigned threads = std::thread::hardware_concurrency();
+  if (const char *e = std::getenv("CGB_MM_THREADS")) threads = (unsigned)std::max(1, std::atoi(e));
+  const size_t len = (size_t)(end - p);
+  threads = (unsigned)std::max<size_t>(1, std::min<size_t>(threads ? threads : 1, len / (256 * 1024) + 1));
+  std::vector<const char *> cut(threads + 1, end);
+  cut[0] = p;
+  for (unsigned k = 1; k < threads; k++) {
+    const char *q = p + len * k / threads;
+    if (q < cut[k - 1]) q = cut[k - 1];
+    cut[k] = skip_line(q, end); // the chunk starts after the next line end
+  }
+  std::vector<std::vector<int32_t>> pr(threads), pc(threads);
+  std::vector<std::vector<double>> pv(threads);
+  std::vector<char> ok(threads, 1);
+  {
+    std::vector<std::thread> pool;
+    for (unsigned k = 1; k < threads; k++)
+      pool.emplace_back([&, k] { ok[k] = parse_lines(cut[k], cut[k + 1], pr[k], pc[k], pv[k]) ? 1 : 0; });
+    ok[0] = parse_lines(cut[0], cut[1], pr[0], pc[0], pv[0]) ? 1 : 0;
+    for (auto &t : pool) t.join();
+  }
+  bool all_ok = true;
+  for (unsigned k = 0; k < threads; k++) all_ok = all_ok && ok[k];
+  if (all_ok) {
+    size_t total = 0;
+    for (unsigned k = 0; k < threads; k++) total += pr[k].size();
+    ri.resize(total);
+    ci.resize(total);
+    vv.resize(total);
+    size_t o = 0;
+    for (unsigned k = 0; k < threads; k++) {
+      if (pr[k].empty()) continue;
+      std::memcpy(ri.data() + o, pr[k].data(), pr[k].size() * sizeof(int32_t));
+      std::memcpy(ci.data() + o, pc[k].data(), pc[k].size() * sizeof(int32_t));
+      std::memcpy(vv.data() + o, pv[k].data(), pv[k].size() * sizeof(double));
+      o += pr[k].size();
+    }
+  } else { // the reference's loop: whitespace-separated tokens, stop at the first triple that does not parse
+    long a, b;
+    double v;
+    while (true) {
+      const char *q = p;
+      if (!parse_int(q, end, a) || !parse_int(q, end, b) || !parse_double(q, end, v)) break;
+      p = q;
+      ri.push_back((int32_t)a);
+      ci.push_back((int32_t)b);
+      vv.push_back(v);
+    }
+  }
+  ::munmap(map, sz);
+  return CGB_OK;
+}
+
+} // namespace cgb
 
 extern "C" {
 
 int cgb_mm_read(const char *path, cgb_mm **out) {
   if (!path || !out) return cgb::fail(CGB_ERR_INVALID, "cgb_mm_read: NULL argument");
   *out = nullptr;
-  FILE *f = std::fopen(path, "rb");
-  if (!f) return cgb::fail(CGB_ERR_IO, "cgb_mm_read: cannot open '%s'", path);
-  std::fseek(f, 0, SEEK_END);
-  const long sz = std::ftell(f);
-  std::fseek(f, 0, SEEK_SET);
-  std::vector<char> buf((size_t)(sz > 0 ? sz : 0));
-  if (sz > 0 && std::fread(buf.data(), 1, (size_t)sz, f) != (size_t)sz) {
-    std::fclose(f);
-    return cgb::fail(CGB_ERR_IO, "cgb_mm_read: short read on '%s'", path);
-  }
-  std::fclose(f);
-  const char *p = buf.data(), *end = p + buf.size();
-  p = skip_line(p, end);                          // banner
-  p = skip_line(p, end);                          // unconditional discard
-  while (p < end && *p == '%') p = skip_line(p, end); // comments
-  p = skip_line(p, end);                          // size line (unused)
-
   std::vector<int32_t> ri, ci;
   std::vector<double> vv;
   {
-    size_t guess = (size_t)(end - p) / 12 + 16;
-    ri.reserve(guess);
-    ci.reserve(guess);
-    vv.reserve(guess);
+    const int rc = cgb::mm_parse_triplets(path, ri, ci, vv);
+    if (rc != CGB_OK) return rc;
   }
-  long a, b;
-  double v;
-  while (true) {
-    const char *q = p;
-    if (!parse_int(q, end, a) || !parse_int(q, end, b) || !parse_double(q, end, v)) break;
-    p = q;
-    ri.push_back((int32_t)(a - 1));
-    ci.push_back((int32_t)(b - 1));
-    vv.push_back(v);
-  }
+  for (auto &x : ri) x -= 1; // 1-based in the file (test/mm_reader.cpp:62-66)
+  for (auto &x : ci) x -= 1;
   const size_t h = ri.size();
   if (h == 0) return cgb::fail(CGB_ERR_IO, "cgb_mm_read: no entries in '%s'", path);
   int32_t lo = ri[0], hi = ri[0];

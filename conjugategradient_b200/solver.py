@@ -64,7 +64,7 @@ class Context:
         return p.value
 
     def free(self, ptr):
-        if ptr:
+        if ptr and self.h:  # after close() there is no stream to order the free on (the driver reclaims at exit)
             L.check(self.lib.cgb_free(self.h, ptr))
 
 
@@ -141,6 +141,22 @@ class Matrix:
         return cls(ctx, handle=h)
 
     @classmethod
+    def from_triplets(cls, ctx: Context, rows, cols, vals, n: int = -1, flags: int = 0):
+        """COO -> CSR on the GPU (cgb_csr_from_triplets; replaces the reference reader's host assembly,
+        test/mm_reader.cpp:45-107, and its HiFlow3 bridge, src/CG.hpp:104-151)."""
+        rows, cols, vals = _i32(rows), _i32(cols), _f64(vals)
+        h = C.c_void_p()
+        L.check(ctx.lib.cgb_csr_from_triplets(ctx.h, n, vals.size, _p(rows), _p(cols), _p(vals), flags, C.byref(h)))
+        return cls(ctx, handle=h)
+
+    @classmethod
+    def from_mm_file(cls, ctx: Context, path: str):
+        """Matrix Market file -> device CSR (parallel parse on the host, assembly on the GPU)."""
+        h = C.c_void_p()
+        L.check(ctx.lib.cgb_csr_from_mm_file(ctx.h, path.encode(), C.byref(h)))
+        return cls(ctx, handle=h)
+
+    @classmethod
     def random_spd(cls, ctx: Context, n: int, seed: int = 12345, d_min: int = 2, d_max: int = 4096, gamma: float = 2.2,
                    row_begin: int = 0, row_end: int = -1):
         """Random SPD matrix with power-law row lengths generated on the device (config C5)."""
@@ -180,9 +196,9 @@ class Matrix:
         return int(self.ctx.lib.cgb_csr_sell_padded(self.h))
 
     def free(self):
-        if self.h:
+        if self.h and self.ctx.h:  # a handle that outlives its context (closed first) must not touch it
             self.ctx.lib.cgb_csr_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         try:

@@ -20,6 +20,7 @@
 #include <cstddef>
 #include <memory>
 #include <type_traits>
+#include <string>
 #include <vector>
 
 namespace CGSolver {
@@ -115,6 +116,24 @@ public:
     m._columns = std::shared_ptr<int[]>(keep, cgb_csr_cols(h));
     m._rows = std::shared_ptr<int[]>(keep, cgb_csr_rowptr(h));
     return m;
+  }
+
+  // Assemble on the GPU from triplets (cgb_csr_from_triplets; flags: CGB_COO_*).  This is the bulk replacement
+  // for the reference's element-by-element HiFlow3 bridge (src/CG.hpp:104-151): hand over (i, j, v) lists once.
+  static Matrix from_triplets(asycl::queue q, const std::vector<int> &rows, const std::vector<int> &cols,
+                              const std::vector<DT> &vals, long long n = -1, int flags = 0) {
+    static_assert(std::is_same<DT, double>::value, "the cgb200 kernels are fp64");
+    cgb_csr *h = nullptr;
+    asycl::detail::check(cgb_csr_from_triplets(q.native(), (int64_t)n, (int64_t)vals.size(), rows.data(), cols.data(),
+                                               vals.data(), flags, &h));
+    return from_handle(q, h);
+  }
+  // Matrix Market file straight to the device, in the dialect of the reference's read_file
+  // (test/mm_reader.cpp:154-171): parallel parse on the host, assembly on the GPU, no host CSR.
+  static Matrix from_file(asycl::queue q, const std::string &path) {
+    cgb_csr *h = nullptr;
+    asycl::detail::check(cgb_csr_from_mm_file(q.native(), path.c_str(), &h));
+    return from_handle(q, h);
   }
 
 private:

@@ -221,6 +221,27 @@ const int32_t *cgb_mm_cols(const cgb_mm *m);
 const int32_t *cgb_mm_rowptr(const cgb_mm *m);
 int cgb_mm_free(cgb_mm *m);
 
+/* ---- triplets (COO) -> device CSR ---------------------------------------------------------------
+ * replaces: the CSR assembly inside the reference reader (test/mm_reader.cpp:45-107: vector of tuples, mirror,
+ * std::sort, row walk) and the element-by-element HiFlow3 bridge (src/CG.hpp:104-151) with one upload and a
+ * radix sort + scans on the GPU.  Output: rows ascending, columns ascending inside a row. */
+enum {
+  CGB_COO_MIRROR = 1,         /* add (j, i, v) for every off-diagonal (i, j, v): one stored triangle -> full matrix */
+  CGB_COO_SUM_DUPLICATES = 2, /* equal (i, j) are summed in input order (finite-element assembly); else kept as they are */
+  CGB_COO_COMPACT_ROWS = 4,   /* a row offset per DISTINCT row id: empty rows vanish, n = number of distinct rows */
+  CGB_COO_ONE_BASED = 8,      /* indices start at 1 */
+  CGB_COO_REFERENCE_DIALECT = 1 | 4 | 8 /* what read_file does to a Matrix Market body (test/mm_reader.cpp:62-104) */
+};
+/* n_rows: matrix dimension, or -1 = largest index + 1 (must be -1 with CGB_COO_COMPACT_ROWS). */
+int cgb_csr_from_triplets(cgb_ctx *ctx, int64_t n_rows, int64_t count, const int32_t *h_rows, const int32_t *h_cols,
+                          const double *h_vals, int flags, cgb_csr **out);
+int cgb_csr_from_triplets_device(cgb_ctx *ctx, int64_t n_rows, int64_t count, const int32_t *d_rows, const int32_t *d_cols,
+                                 const double *d_vals, int flags, cgb_csr **out);
+/* Matrix Market file -> device CSR without a host CSR in between: the body is parsed on all host cores
+ * (same dialect as cgb_mm_read / the reference's read_file), assembled on the GPU.  Same arrays as
+ * cgb_mm_read + cgb_csr_create on well-formed files (no duplicate coordinates). */
+int cgb_csr_from_mm_file(cgb_ctx *ctx, const char *path, cgb_csr **out);
+
 /* ---- row-partitioned multi-GPU (new; the reference is single-device) -------------------------
  * One process per GPU.  Rank r owns the contiguous global rows [row_begin, row_end); its local
  * CSR (cgb_csr with n = row_end-row_begin rows and GLOBAL column indices) is split into interior

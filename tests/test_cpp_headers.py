@@ -125,3 +125,19 @@ def test_tester_rel_tolerance_iterations(tmp_path, port):
     info = out.stderr.split()
     iters = int(info[info.index("iterations") + 1])
     assert abs(iters - 366) <= 7                             # SURVEY.md §8c probe: 366 (+-2 %)
+
+
+@pytest.mark.gpu
+def test_tester_device_ingest_equals_host_ingest(tmp_path):
+    """`tester file rel:1e-8 device` (Matrix::from_file: GPU assembly) against the read_file + setMatrix path."""
+    _built()
+    v, c, r = G.random_spd_powerlaw(20000, seed=6)
+    p = str(tmp_path / "r.mtx")
+    G.write_mtx_reference_dialect(p, v, c, r)
+    outs = []
+    for extra in ([], ["device"]):
+        o = subprocess.run([TESTER, p, "rel:1e-10"] + extra, capture_output=True, text=True, check=True)
+        dim, nnz, ms, acc = o.stdout.split()
+        info = o.stderr.split()
+        outs.append((int(dim), int(nnz), float(acc), int(info[info.index("iterations") + 1])))
+    assert outs[0] == outs[1] and outs[0][:2] == (20000, v.size)   # same arrays -> same solve, bit for bit

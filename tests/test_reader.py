@@ -55,3 +55,33 @@ def test_reader_missing_file_is_an_error_not_an_abort():
     with pytest.raises(L.CgbError) as e:
         S.mm_read("/nonexistent/file.mtx")
     assert e.value.code == L.CGB_ERR_IO
+
+
+def test_reader_parallel_parse_equals_serial(tmp_path, port, monkeypatch):
+    """A body large enough to be cut into several line-aligned chunks parses to the same arrays as one thread
+    and as the oracle's reader (which follows the reference's token loop, test/mm_reader.cpp:62-66)."""
+    v, c, r = G.random_spd_powerlaw(40000, seed=4)
+    p = str(tmp_path / "big.mtx")
+    G.write_mtx_reference_dialect(p, v, c, r)
+    assert os.path.getsize(p) > 4 * 256 * 1024
+    monkeypatch.setenv("CGB_MM_THREADS", "7")
+    many = S.mm_read(p)
+    monkeypatch.setenv("CGB_MM_THREADS", "1")
+    one = S.mm_read(p)
+    assert same(many, one) and same(many, (v, c, r)) and same(port.mm_read(p), many)
+
+
+def test_reader_odd_layouts_fall_back_to_the_token_stream(tmp_path, ref_serial, monkeypatch):
+    """Triples that straddle lines, and a body that stops parsing half way: the line-parallel fast path must
+    step aside and reproduce the reference's own reading loop."""
+    monkeypatch.setenv("CGB_MM_THREADS", "4")
+    head = "%%MatrixMarket matrix coordinate real symmetric\n%\n4 4 5\n"
+    cases = {
+        "straddle": head + "1 1\n2.0 2 1\n-1 2 2 2\n3 3 2 4 4\n2\n",
+        "stops": head + "1 1 2\n2 1 -1\n2 2 2\nthis is not a number\n3 3 2\n4 4 2\n",
+        "blank_lines": head + "1 1 2\n\n2 1 -1\n   \n2 2 2\n3 3 2\n4 4 2\n\n",
+    }
+    for name, text in cases.items():
+        p = tmp_path / (name + ".mtx")
+        p.write_text(text)
+        assert same(S.mm_read(str(p)), ref_serial.mm_read(str(p))), name

@@ -137,7 +137,7 @@ def run_reference(args, kind, m, rel):
         "e2e": {"value": out["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "setup_s": round(time.time() - t0, 1),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def gen_host_csr(kind, m):
@@ -459,14 +459,28 @@ def run_ours(args, kind, m, rel):
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "achieved_GBps_B_iter": iters * b_iter(n, nnz) / (ms_total * 1e6),
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dh is not None:
         lib.cgb_dist_destroy(dh)
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line, on the process's real stdout (see main)."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    # Libraries write to fd 1 behind Python's back (NCCL prints "NCCL version ..." there on multi-GPU runs): keep
+    # the contract of exactly one JSON line on stdout by pointing fd 1 at stderr for the duration of the run.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)

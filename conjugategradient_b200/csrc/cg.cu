@@ -36,6 +36,8 @@ struct LoopCfg {
   SpmvLaunch sl;
   int grid_vec;
   int grid_pup;
+  bool replace;    // residual replacement at the end of every batch
+  const double *b; // right-hand side (replacement only)
 };
 
 // Enqueue one CG iteration on `s`.  When `timed`, bracket the kernels with external event records
@@ -68,10 +70,23 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
   return CGB_OK;
 }
 
+// End of a batch with residual replacement: flush the pending x update, r = b - A x, rr = r.r, alpha = 0.
+static int enqueue_replacement(cgb_csr *A, double *x, const LoopCfg &c, cudaStream_t s) {
+  Workspace &w = A->ws;
+  cg_xflush_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, x, w.p0, w.p1, c.fused ? 1 : 0, w.st, 1);
+  launch_panel_partials(A, c.sl, s, x, w.r, w.st);
+  dispatch_lanes(c.sl.lanes, c.sl.eng, [&](auto Lc, auto Tc) {
+    launch_kernel(cg_replace_kernel<decltype(Lc)::value, decltype(Tc)::value>, c.sl, s, csr_view_final(A, w.r),
+                  (const double *)x, c.b, w.r, w.st, w.partials);
+  });
+  CGB_CUDA(cudaGetLastError());
+  return CGB_OK;
+}
+
 static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint64_t key) {
   Workspace &w = A->ws;
   cudaStream_t s = A->ctx->stream;
-  if (w.graph && w.graph_key == key && w.graph_x == x) return CGB_OK;
+  if (w.graph && w.graph_key == key && w.graph_x == x && (!c.replace || w.graph_b == c.b)) return CGB_OK;
   if (w.graph) {
     cudaGraphExecDestroy(w.graph);
     w.graph = nullptr;
@@ -80,6 +95,7 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
   CGB_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
   int rc = CGB_OK;
   for (int i = 0; i < batch && rc == CGB_OK; i++) rc = enqueue_iteration(A, x, c, s, c.time_kernels && i == 0);
+  if (rc == CGB_OK && c.replace) rc = enqueue_replacement(A, x, c, s);
   cudaError_t e = cudaStreamEndCapture(s, &g);
   if (rc != CGB_OK) {
     if (g) cudaGraphDestroy(g);
@@ -109,6 +125,7 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
   }
   w.graph_key = key;
   w.graph_x = x;
+  w.graph_b = c.b;
   return CGB_OK;
 }
 
@@ -142,6 +159,8 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
 
   int mode = o.loop_mode;
   int batch = o.check_every > 0 ? o.check_every : 32;
+  const bool replace = o.residual_replace_every > 0;
+  if (replace) batch = o.residual_replace_every; // a batch ends with the replacement
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
   CGB_TRY(csr_prepare(A));
@@ -149,7 +168,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   // system is small enough that latency rules (CGB_PERSISTENT_MAX_N rows); it serves CSR rows only.
   int64_t persistent_max_n = 131072; // measured cross-over on B200: 2D 5-pt 256^2 still wins (89k vs 77k it/s), 512^2 loses
   if (const char *e = getenv("CGB_PERSISTENT_MAX_N")) persistent_max_n = atoll(e);
-  const bool can_persist = ctx->coop_ok && csr_engine(A) != kEngSell && !o.time_kernels;
+  const bool can_persist = !replace && ctx->coop_ok && csr_engine(A) != kEngSell && !o.time_kernels;
   const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
   if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
   const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
@@ -166,7 +185,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
       l2w = false;
     }
   }
-  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup};
+  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, replace, d_b};
   if (l2w) {
     cudaStreamAttrValue v;
     memset(&v, 0, sizeof(v));
@@ -253,7 +272,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
                          (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.eng << 2) ^
-                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)csr_panels(A) << 48);
+                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)replace << 5) ^ ((uint64_t)csr_panels(A) << 48);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an
@@ -274,8 +293,9 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
       CGB_CUDA(cudaGraphLaunch(w.graph, s));
     } else {
       for (int i = 0; i < batch; i++) CGB_TRY(enqueue_iteration(A, d_x, cfg, s, cfg.time_kernels && i == 0));
+      if (replace) CGB_TRY(enqueue_replacement(A, d_x, cfg, s));
     }
-    launches += (int64_t)batch * per_iter;
+    launches += (int64_t)batch * per_iter + (replace ? 2 + extra : 0);
     issued += batch;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[slot], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaEventRecord(polled[slot], s));
@@ -307,7 +327,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   }
   // the x update of the last trip (deferred: see cg_kernels.cuh), then drain and take the final state
   if (!persistent) {
-    cg_xflush_kernel<<<cfg.grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, fused ? 1 : 0, w.st);
+    cg_xflush_kernel<<<cfg.grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, fused ? 1 : 0, w.st, 0);
     CGB_CUDA(cudaGetLastError());
     launches += 1;
   }

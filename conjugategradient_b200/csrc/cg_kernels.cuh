@@ -95,6 +95,32 @@ __global__ void CGB_BOUNDS(ENG) cg_init_kernel(CsrView A, const double *__restri
   }
 }
 
+// ---- residual replacement (optional; not in the reference) ------------------------------------------
+// r = b - A x recomputed from the current iterate, rr = r.r: run every `residual_replace_every` trips, after the
+// pending x update has been flushed.  The recurrence residual the reference iterates on (src/CG.hpp:392-416)
+// drifts away from b - A x once rounding dominates (972 trips at Tester's 1e-24 with the true
+// residual stuck at 2.8e-12); replacing it keeps the stop rule honest.  alpha is cleared because the flush has
+// already applied it (the next p-update would apply it again).
+template <int L, int ENG>
+__global__ void CGB_BOUNDS(ENG) cg_replace_kernel(CsrView A, const double *__restrict__ x, const double *__restrict__ b,
+                                                  double *r, CgState *st, double *partials) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  double a0 = 0.0, a1 = 0.0;
+  GatherPlain g{x};
+  EpiInitResidual e{b, r};
+  spmv_rows<L, ENG>(A, g, e, a0, a1);
+  a0 = block_sum(a0, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = a0;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rr = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      st->rr = rr;
+      st->alpha = 0.0;
+    }
+  }
+}
+
 // ---- K3 (unfused only) -------------------------------------------------------------------------
 static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, const double *__restrict__ r,
                                                              double *__restrict__ p, double *__restrict__ x,
@@ -235,8 +261,9 @@ static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, dou
 // Launched once after the loop; p of the last trip is pbuf0 (unfused) or the buffer the parity
 // of the trip counter selects (fused).
 static __global__ void __launch_bounds__(kBlock) cg_xflush_kernel(int64_t n, double *__restrict__ x, const double *pbuf0,
-                                                            const double *pbuf1, int fused, const CgState *st) {
+                                                            const double *pbuf1, int fused, const CgState *st, int gated) {
   if (st->iter <= 0) return; // no trip ran: nothing pending
+  if (gated && !cg_active(st)) return; // inside the loop (residual replacement): the flush after the loop does the last trip
   const double alpha = st->alpha;
   const double *p = (fused && (st->iter & 1)) ? pbuf1 : pbuf0;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;

@@ -12,6 +12,7 @@
 // DISTINCT row id, so empty rows vanish (:92-104).
 #include "matrix.cuh"
 
+#include <chrono>
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
@@ -231,7 +232,8 @@ int coo_to_csr_device(cgb_ctx *ctx, int64_t n_rows, int64_t h, const int *d_r, c
 
 namespace cgb {
 // mm_reader.cpp: the reference dialect's triplets (1-based) of a Matrix Market file, parsed on all host cores
-int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv);
+int mm_parse_chunks(const char *path, std::vector<std::vector<int32_t>> &pr, std::vector<std::vector<int32_t>> &pc,
+                    std::vector<std::vector<double>> &pv);
 } // namespace cgb
 
 extern "C" {
@@ -264,11 +266,39 @@ int cgb_csr_from_triplets(cgb_ctx *ctx, int64_t n_rows, int64_t count, const int
 int cgb_csr_from_mm_file(cgb_ctx *ctx, const char *path, cgb_csr **out) {
   CGB_REQUIRE(ctx && path && out, "cgb_csr_from_mm_file: NULL argument");
   *out = nullptr;
-  std::vector<int32_t> ri, ci;
-  std::vector<double> vv;
-  CGB_TRY(mm_parse_triplets(path, ri, ci, vv));
-  if (ri.empty()) return fail(CGB_ERR_IO, "cgb_csr_from_mm_file: no entries in '%s'", path);
-  return cgb_csr_from_triplets(ctx, -1, (int64_t)ri.size(), ri.data(), ci.data(), vv.data(), CGB_COO_REFERENCE_DIALECT, out);
+  std::vector<std::vector<int32_t>> pr, pc;
+  std::vector<std::vector<double>> pv;
+  const bool timing = getenv("CGB_INGEST_TIMING") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  CGB_TRY(mm_parse_chunks(path, pr, pc, pv));
+  const auto t1 = std::chrono::steady_clock::now();
+  size_t total = 0;
+  for (auto &x : pr) total += x.size();
+  if (total == 0) return fail(CGB_ERR_IO, "cgb_csr_from_mm_file: no entries in '%s'", path);
+  CGB_REQUIRE(total < ((size_t)1 << 31), "cgb_csr_from_mm_file: too many entries for 32-bit offsets");
+  // the parser's per-thread chunks go up as they are (no concatenation on the host)
+  ScopedDevice sd(ctx->device);
+  Buf r, c, v;
+  CGB_CUDA(cudaMalloc(&r.p, sizeof(int) * total));
+  CGB_CUDA(cudaMalloc(&c.p, sizeof(int) * total));
+  CGB_CUDA(cudaMalloc(&v.p, sizeof(double) * total));
+  size_t o = 0;
+  for (size_t k = 0; k < pr.size(); k++) {
+    const size_t m = pr[k].size();
+    if (m == 0) continue;
+    CGB_CUDA(cudaMemcpyAsync(r.as<int>() + o, pr[k].data(), sizeof(int) * m, cudaMemcpyHostToDevice, ctx->stream));
+    CGB_CUDA(cudaMemcpyAsync(c.as<int>() + o, pc[k].data(), sizeof(int) * m, cudaMemcpyHostToDevice, ctx->stream));
+    CGB_CUDA(cudaMemcpyAsync(v.as<double>() + o, pv[k].data(), sizeof(double) * m, cudaMemcpyHostToDevice, ctx->stream));
+    o += m;
+  }
+  const int rc = cgb_csr_from_triplets_device(ctx, -1, (int64_t)total, r.as<int>(), c.as<int>(), v.as<double>(),
+                                              CGB_COO_REFERENCE_DIALECT, out);
+  if (timing) {
+    const auto t2 = std::chrono::steady_clock::now();
+    fprintf(stderr, "cgb_csr_from_mm_file: parse %.3f s (%zu chunks), upload + GPU assembly %.3f s (%zu triplets)\n",
+            std::chrono::duration<double>(t1 - t0).count(), pr.size(), std::chrono::duration<double>(t2 - t1).count(), total);
+  }
+  return rc;
 }
 
 } // extern "C"

@@ -480,7 +480,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   if (w.h_st[0].comm_error)
     return fail(CGB_ERR_NCCL, "cgb_dist_cg_solve: a peer did not answer within the time limit (rank %d, trip %lld)", d->rank,
                 (long long)w.h_st[0].iter);
-  if (n > 0) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st); // last trip's x update
+  if (n > 0) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st, 0); // last trip's x update
   CGB_CUDA(cudaGetLastError());
   launches += 1;
   CGB_CUDA(cudaEventRecord(t1, s));

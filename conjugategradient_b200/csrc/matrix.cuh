@@ -26,6 +26,7 @@ struct Workspace {
   cudaGraphExec_t graph = nullptr;
   uint64_t graph_key = 0;
   const double *graph_x = nullptr; // the x pointer baked into the graph
+  const double *graph_b = nullptr; // the b pointer baked into it (residual replacement only)
   // kernel timing events (time_kernels)
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };

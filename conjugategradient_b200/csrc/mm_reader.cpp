@@ -69,7 +69,12 @@ inline bool parse_double(const char *&p, const char *end, double &out) {
 // One chunk of the body, line-aligned: every non-blank line must be exactly "i j v".  Returns false when a line
 // does not fit that shape (the caller then re-parses the whole body as a token stream, which is the reference's
 // own reading loop, test/mm_reader.cpp:62-66).
-bool parse_lines(const char *p, const char *end, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv) {
+bool parse_lines(const char *p, const char *end, std::vector<int32_t> &ri_out, std::vector<int32_t> &ci_out,
+                 std::vector<double> &vv_out) {
+  // thread-local vectors, handed over at the end: the callers' vector headers sit next to each other in memory,
+  // and push_back rewrites the header on every line (false sharing made 2 threads slower than 1)
+  std::vector<int32_t> ri, ci;
+  std::vector<double> vv;
   const size_t guess = (size_t)(end - p) / 12 + 16;
   ri.reserve(guess);
   ci.reserve(guess);
@@ -90,6 +95,9 @@ bool parse_lines(const char *p, const char *end, std::vector<int32_t> &ri, std::
     ci.push_back((int32_t)b);
     vv.push_back(v);
   }
+  ri_out = std::move(ri);
+  ci_out = std::move(ci);
+  vv_out = std::move(vv);
   return true;
 }
 
@@ -97,13 +105,14 @@ bool parse_lines(const char *p, const char *end, std::vector<int32_t> &ri, std::
 
 namespace cgb {
 
-// Body of a Matrix Market file in the reference dialect -> 1-based triplets, in file order.  The file is mapped,
+// Body of a Matrix Market file in the reference dialect -> 1-based triplets, in file order, one chunk per thread.  The file is mapped,
 // cut at line ends into one chunk per host thread and parsed with from_chars; files whose lines are not plain
 // "i j v" fall back to the serial token stream.
-int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv) {
-  ri.clear();
-  ci.clear();
-  vv.clear();
+int mm_parse_chunks(const char *path, std::vector<std::vector<int32_t>> &pr, std::vector<std::vector<int32_t>> &pc,
+                    std::vector<std::vector<double>> &pv) {
+  pr.clear();
+  pc.clear();
+  pv.clear();
   const int fd = ::open(path, O_RDONLY);
   if (fd < 0) return fail(CGB_ERR_IO, "cgb_mm_read: cannot open '%s'", path);
   struct stat st;
@@ -137,9 +146,10 @@ int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<in
     if (q < cut[k - 1]) q = cut[k - 1];
     cut[k] = skip_line(q, end); // the chunk starts after the next line end
   }
-  std::vector<std::vector<int32_t>> pr(threads), pc(threads);
-  std::vector<std::vector<double>> pv(threads);
-  std::vector<char> ok(threads, 1);
+  pr.resize(threads);
+  pc.resize(threads);
+  pv.resize(threads);
+  std::vector<int> ok(threads, 1);
   {
     std::vector<std::thread> pool;
     for (unsigned k = 1; k < threads; k++)
@@ -149,33 +159,45 @@ int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<in
   }
   bool all_ok = true;
   for (unsigned k = 0; k < threads; k++) all_ok = all_ok && ok[k];
-  if (all_ok) {
-    size_t total = 0;
-    for (unsigned k = 0; k < threads; k++) total += pr[k].size();
-    ri.resize(total);
-    ci.resize(total);
-    vv.resize(total);
-    size_t o = 0;
-    for (unsigned k = 0; k < threads; k++) {
-      if (pr[k].empty()) continue;
-      std::memcpy(ri.data() + o, pr[k].data(), pr[k].size() * sizeof(int32_t));
-      std::memcpy(ci.data() + o, pc[k].data(), pc[k].size() * sizeof(int32_t));
-      std::memcpy(vv.data() + o, pv[k].data(), pv[k].size() * sizeof(double));
-      o += pr[k].size();
-    }
-  } else { // the reference's loop: whitespace-separated tokens, stop at the first triple that does not parse
+  if (!all_ok) { // the reference's loop: whitespace-separated tokens, stop at the first triple that does not parse
+    pr.assign(1, {});
+    pc.assign(1, {});
+    pv.assign(1, {});
     long a, b;
     double v;
     while (true) {
       const char *q = p;
       if (!parse_int(q, end, a) || !parse_int(q, end, b) || !parse_double(q, end, v)) break;
       p = q;
-      ri.push_back((int32_t)a);
-      ci.push_back((int32_t)b);
-      vv.push_back(v);
+      pr[0].push_back((int32_t)a);
+      pc[0].push_back((int32_t)b);
+      pv[0].push_back(v);
     }
   }
   ::munmap(map, sz);
+  return CGB_OK;
+}
+
+
+// the same, concatenated in file order
+int mm_parse_triplets(const char *path, std::vector<int32_t> &ri, std::vector<int32_t> &ci, std::vector<double> &vv) {
+  std::vector<std::vector<int32_t>> pr, pc;
+  std::vector<std::vector<double>> pv;
+  const int rc = mm_parse_chunks(path, pr, pc, pv);
+  if (rc != CGB_OK) return rc;
+  size_t total = 0;
+  for (auto &x : pr) total += x.size();
+  ri.resize(total);
+  ci.resize(total);
+  vv.resize(total);
+  size_t o = 0;
+  for (size_t k = 0; k < pr.size(); k++) {
+    if (pr[k].empty()) continue;
+    std::memcpy(ri.data() + o, pr[k].data(), pr[k].size() * sizeof(int32_t));
+    std::memcpy(ci.data() + o, pc[k].data(), pc[k].size() * sizeof(int32_t));
+    std::memcpy(vv.data() + o, pv[k].data(), pv[k].size() * sizeof(double));
+    o += pr[k].size();
+  }
   return CGB_OK;
 }
 

@@ -168,7 +168,12 @@ typedef struct cgb_cg_opts {
   int time_kernels;     /* 1: bracket the kernels of one iteration per batch with CUDA events */
   int l2_persist_p;     /* 1: L2 persisting access-policy window over the gathered vector */
   int record_history;   /* 1: keep r.r after every iteration (read with cgb_cg_history) */
-  int reserved[6];
+  int residual_replace_every; /* k > 0: every k iterations r is recomputed as b - A x (true residual) and rr
+                           from it, so the stop rule cannot run ahead of the real residual the way the
+                           reference's recurrence does at tight tolerances; one extra
+                           SpMV per k iterations; single-GPU graph / stepwise loops.  0 (default): classical
+                           recurrence, as the reference */
+  int reserved[5];
 } cgb_cg_opts;
 
 typedef struct cgb_cg_stats {

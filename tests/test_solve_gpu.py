@@ -206,3 +206,36 @@ def test_full_size_properties_C2(ctx):
     st2 = cg2.solve(2e-8 * nb)
     assert st2["iterations"] == st["iterations"]
     assert rel_err(cg2.extract(), 2 * x1) <= 1e-12
+
+
+@pytest.mark.parametrize("fused", [0, 1])
+def test_residual_replacement_keeps_the_stop_rule_honest(ctx, port, fused):
+    """Additive option (not in the reference): at a tolerance below what fp64 can reach, the reference's recurrence
+    residual keeps shrinking while b - A x stagnates (972 trips at Tester's 1e-24, true residual
+    2.8e-12 * |b|).  With r recomputed every 20 trips the reported residual IS the true one."""
+    v, c, r = G.poisson2d_5pt(128)
+    n = r.size - 1
+    b = G.default_rhs(n)
+    nb = np.linalg.norm(b)
+    tol = 1e-16 * nb
+    plain = S.CG(ctx, fuse_p_update=fused)
+    plain.setMatrix(v, c, r)
+    plain.setTarget(b)
+    st0 = plain.solve(tol, max_iter=3000)
+    true0 = np.sqrt(plain.residual()[0])
+    assert st0["converged"] == 1 and np.sqrt(st0["rr"]) <= tol and true0 > 1e3 * tol      # the recurrence ran ahead
+    rep = S.CG(ctx, fuse_p_update=fused, residual_replace_every=20)
+    rep.setMatrix(v, c, r)
+    rep.setTarget(b)
+    st1 = rep.solve(tol, max_iter=3000)
+    true1 = np.sqrt(rep.residual()[0])
+    assert st1["iterations"] == 3000 and st1["converged"] == 0                           # honest: 1e-16 is out of reach
+    assert true1 <= true0 / 3                              # and the iterate is better for it (measured: 1.2e-13 vs 2.8e-12)
+    # at a reachable tolerance both variants stop within a batch of each other and agree with the oracle
+    tol = 1e-8 * nb
+    o = port.cg_solve(v, c, r, b, tol)
+    rep.x = None
+    st2 = rep.solve(tol)
+    assert st2["converged"] == 1 and abs(st2["iterations"] - o["iterations"]) <= 20
+    assert rel_err(rep.extract(), o["x"]) <= 1e-8
+    assert np.sqrt(rep.residual()[0]) <= 1.01 * tol + 1e-9 * nb

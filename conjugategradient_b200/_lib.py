@@ -17,8 +17,8 @@ c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)
 c_vp = C.c_void_p
 
-CGB_OK, CGB_ERR_INVALID, CGB_ERR_CUDA, CGB_ERR_NCCL, CGB_ERR_STATE, CGB_ERR_IO = range(6)
-FMT_AUTO, FMT_CSR, FMT_SELL = 0, 1, 2
+CGB_OK, CGB_ERR_INVALID, CGB_ERR_CUDA, CGB_ERR_NCCL, CGB_ERR_STATE, CGB_ERR_IO, CGB_ERR_UNSUPPORTED = range(7)
+FMT_AUTO, FMT_CSR, FMT_SELL, FMT_DICT = 0, 1, 2, 3
 COO_MIRROR, COO_SUM_DUPLICATES, COO_COMPACT_ROWS, COO_ONE_BASED = 1, 2, 4, 8
 COO_REFERENCE_DIALECT = COO_MIRROR | COO_COMPACT_ROWS | COO_ONE_BASED
 LOOP_AUTO, LOOP_GRAPH, LOOP_PERSISTENT, LOOP_STEPWISE = 0, 1, 2, 3
@@ -81,6 +81,8 @@ SIGNATURES = {
     "cgb_csr_rowptr": (c_vp, [c_vp]),
     "cgb_csr_build_sell": (C.c_int, [c_vp, C.c_int]),
     "cgb_csr_sell_padded": (c_i64, [c_vp]),
+    "cgb_csr_dict_bytes": (c_i64, [c_vp]),
+    "cgb_csr_dict_patterns": (C.c_int, [c_vp]),
     "cgb_csr_set_format": (C.c_int, [c_vp, C.c_int]),
     "cgb_csr_get_format": (C.c_int, [c_vp]),
     "cgb_csr_set_panels": (C.c_int, [c_vp, C.c_int]),

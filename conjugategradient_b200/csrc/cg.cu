@@ -168,7 +168,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   // system is small enough that latency rules (CGB_PERSISTENT_MAX_N rows); it serves CSR rows only.
   int64_t persistent_max_n = 131072; // measured cross-over on B200: 2D 5-pt 256^2 still wins (89k vs 77k it/s), 512^2 loses
   if (const char *e = getenv("CGB_PERSISTENT_MAX_N")) persistent_max_n = atoll(e);
-  const bool can_persist = !replace && ctx->coop_ok && csr_engine(A) != kEngSell && !o.time_kernels;
+  const bool can_persist = !replace && ctx->coop_ok && (csr_engine(A) == kEngTma || csr_engine(A) == kEngVec) && !o.time_kernels;
   const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
   if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
   const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
@@ -353,7 +353,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     }
     stats->kernel_launches = launches;
     stats->loop_mode = mode;
-    stats->format = cfg.sl.eng == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
+    stats->format = cfg.sl.eng == kEngSell ? CGB_FMT_SELL : cfg.sl.eng == kEngDict ? CGB_FMT_DICT : CGB_FMT_CSR;
   }
   return CGB_OK;
 }

@@ -19,6 +19,7 @@
 // stop test has fired or the trip cap is reached, later launches return immediately, so a CUDA
 // graph holding a batch of iterations can overshoot harmlessly.
 #pragma once
+#include "spmv_dict.cuh"
 #include "spmv_tma.cuh"
 
 namespace cgb {
@@ -41,6 +42,8 @@ struct CsrView {
   const int64_t *sell_chunk;
   // column panels (kEngSell): when set, the row sum handed to the epilogue is panel_acc[row] + (this panel's sum)
   const double *panel_acc;
+  // row-pattern dictionary copy (engine kEngDict only)
+  DictView dict;
 };
 
 // One entry point for the three row engines: CSR with direct loads and L lanes per row (256 threads),
@@ -54,6 +57,9 @@ __device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E 
   } else if constexpr (ENG == kEngSell) {
     spmv_rows_sell(A.n, A.sell_slices, A.sell_off, A.sell_width, A.sell_cols, A.sell_vals, A.sell_perm, A.sell_nlong, A.sell_long,
                    A.sell_chunk, A.rowptr, A.cols, A.vals, A.panel_acc, g, e, blockIdx.x, gridDim.x, a0, a1);
+  } else if constexpr (ENG == kEngDict) {
+    extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
+    spmv_rows_dict(A.n, A.dict, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
   } else {
     spmv_rows_vec<L>(0, A.n, A.rowptr, A.cols, A.vals, g, e, blockIdx.x, gridDim.x, a0, a1);
   }

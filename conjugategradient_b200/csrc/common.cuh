@@ -34,7 +34,7 @@ int fail(int code, const char *fmt, ...);
     if (!(cond)) return ::cgb::fail(CGB_ERR_INVALID, "%s", msg);    \
   } while (0)
 
-constexpr int kEngVec = 0, kEngTma = 1, kEngSell = 2; // row engines of the SpMV-shaped kernels
+constexpr int kEngVec = 0, kEngTma = 1, kEngSell = 2, kEngDict = 3; // row engines of the SpMV-shaped kernels
 constexpr int kSellLongRow = 256; // rows longer than this stay out of the SELL slices (sell.cu)
 constexpr int kBlock = 256;        // threads per CTA for every streaming kernel
 constexpr int kMaxPartials = 4096; // upper bound on CTAs that take part in a reduction

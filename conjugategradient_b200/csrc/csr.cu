@@ -4,6 +4,8 @@
 // VectorOperations::spmv (src/VectorOperations.hpp:438-466), CG::accuracy (src/CG.hpp:463-515).
 #include "launch.cuh"
 
+#include <algorithm>
+
 #include <cub/device/device_scan.cuh>
 #include <stdlib.h>
 
@@ -25,6 +27,11 @@ int csr_plan(cgb_csr *A) {
   if (const char *e = getenv("CGB_SELL_CTAS")) sell_per_sm = atoi(e) > 0 ? atoi(e) : sell_per_sm;
   A->grid_sell = sms * sell_per_sm;
   if (A->grid_sell > kMaxPartials) A->grid_sell = kMaxPartials;
+  int occ_d = 8; // dictionary engine: a thread per row, grid-stride, one resident wave
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_d, cg_spmv_kernel<1, kEngDict, false>, kBlock, 0);
+  if (const char *e = getenv("CGB_DICT_CTAS")) occ_d = atoi(e) > 0 ? atoi(e) : occ_d;
+  A->grid_dict = sms * (occ_d > 0 ? occ_d : 1);
+  if ((A->n + kBlock - 1) / kBlock < A->grid_dict) A->grid_dict = (int)std::max<int64_t>(1, (A->n + kBlock - 1) / kBlock);
   if ((A->n + 255) / 256 < A->grid_sell) A->grid_sell = (int)((A->n + 255) / 256 > 0 ? (A->n + 255) / 256 : 1);
   // streaming vector kernels: exactly one resident wave (grid-stride loops), so no partial second wave
   // leaves SMs idle at the tail; CGB_VEC_CTAS caps the CTAs per SM for A/B measurements
@@ -104,6 +111,7 @@ int csr_prepare(cgb_csr *A) {
     A->auto_sell = A->n >= 4096 && (A->overflow_tiles * 50 > ntiles || (double)A->max_row > 8.0 * mean + 64.0);
     if (const char *env = getenv("CGB_AUTO_SELL")) A->auto_sell = atoi(env) != 0;
   }
+  if (A->format == CGB_FMT_DICT && !A->dict_ids) CGB_TRY(csr_build_dict(A));
   if (csr_wants_sell(A)) {
     // Column panels: the gathered vector is read at random columns; when it is larger than what L2 keeps
     // (the matrix streams through with evict-first, but a B200 L2 half holds ~60 MB), most gathers go to
@@ -287,6 +295,7 @@ int cgb_csr_destroy(cgb_csr *A) {
   cudaStreamSynchronize(A->ctx->stream);
   workspace_release(A);
   csr_release_panels(A);
+  csr_release_dict(A);
   cudaFree(A->sell_vals);
   cudaFree(A->sell_cols);
   cudaFree(A->sell_off);
@@ -311,13 +320,21 @@ int32_t *cgb_csr_rowptr(cgb_csr *A) { return A ? A->rowptr : nullptr; }
 
 int cgb_csr_set_format(cgb_csr *A, int format) {
   CGB_REQUIRE(A, "cgb_csr_set_format: NULL matrix");
-  CGB_REQUIRE(format == CGB_FMT_AUTO || format == CGB_FMT_CSR || format == CGB_FMT_SELL, "unknown format");
+  CGB_REQUIRE(format == CGB_FMT_AUTO || format == CGB_FMT_CSR || format == CGB_FMT_SELL || format == CGB_FMT_DICT,
+              "unknown format");
   if (format != A->format && A->ws.graph) { // cached graphs hold the other engine's kernels
     cudaGraphExecDestroy(A->ws.graph);
     A->ws.graph = nullptr;
   }
+  const int before = A->format;
   A->format = format;
-  if (format == CGB_FMT_SELL) CGB_TRY(csr_prepare(A)); // builds the SELL copy (or the column panels) now
+  if (format == CGB_FMT_SELL || format == CGB_FMT_DICT) { // builds the SELL copy / column panels / packed copy now
+    const int rc = csr_prepare(A);
+    if (rc != CGB_OK) {
+      A->format = before; // e.g. CGB_ERR_UNSUPPORTED: the matrix keeps streaming the way it did
+      return rc;
+    }
+  }
   return CGB_OK;
 }
 int cgb_csr_get_format(const cgb_csr *A) { return A ? A->format : 0; }

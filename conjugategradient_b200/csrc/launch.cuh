@@ -22,6 +22,7 @@ inline bool csr_wants_sell(const cgb_csr *A) {
 inline size_t csr_panels(const cgb_csr *A) { return csr_wants_sell(A) ? A->panels.size() : 0; }
 
 inline int csr_engine(const cgb_csr *A) {
+  if (A->format == CGB_FMT_DICT && A->dict_ids) return kEngDict;
   if (csr_wants_sell(A) && (A->sell_vals || !A->panels.empty())) return kEngSell;
   return A->use_tma ? kEngTma : kEngVec;
 }
@@ -29,22 +30,27 @@ inline int csr_engine(const cgb_csr *A) {
 inline SpmvLaunch spmv_launch_cfg(const cgb_csr *A) {
   SpmvLaunch c;
   c.eng = csr_engine(A);
-  c.lanes = c.eng == kEngTma ? A->lanes_tma : (c.eng == kEngSell ? 1 : A->lanes);
-  c.grid = c.eng == kEngTma ? A->grid_tma : (c.eng == kEngSell ? A->grid_sell : A->grid_spmv);
+  c.lanes = c.eng == kEngTma ? A->lanes_tma : ((c.eng == kEngSell || c.eng == kEngDict) ? 1 : A->lanes);
+  c.grid = c.eng == kEngTma ? A->grid_tma : c.eng == kEngSell ? A->grid_sell : c.eng == kEngDict ? A->grid_dict : A->grid_spmv;
   c.block = c.eng == kEngTma ? kTmaThreads : kBlock;
-  c.smem = c.eng == kEngTma ? tma_smem_bytes(kTmaConsumers / c.lanes) : 0;
+  c.smem = c.eng == kEngTma ? tma_smem_bytes(kTmaConsumers / c.lanes) : c.eng == kEngDict ? dict_smem_bytes(A->dict_npat, A->dict_nent) : 0;
   return c;
 }
 
 inline CsrView csr_view(const cgb_csr *A) {
   return CsrView{A->n, A->nnz, A->rowptr, A->cols, A->vals, A->sell_slices, A->sell_off, A->sell_width, A->sell_cols, A->sell_vals, A->sell_perm,
-                 A->sell_nlong, A->sell_long, A->sell_chunk, nullptr};
+                 A->sell_nlong, A->sell_long, A->sell_chunk, nullptr,
+                 DictView{A->dict_ids, A->dict_ptr, A->dict_off, A->dict_val, A->dict_npat, A->dict_nent}};
 }
 
 // f(std::integral_constant<int, L>, std::integral_constant<int, ENG>)
 template <class F> inline void dispatch_lanes(int lanes, int eng, F &&f) {
   if (eng == kEngSell) {
     f(std::integral_constant<int, 1>{}, std::integral_constant<int, kEngSell>{});
+    return;
+  }
+  if (eng == kEngDict) {
+    f(std::integral_constant<int, 1>{}, std::integral_constant<int, kEngDict>{});
     return;
   }
 #define CGB_CASE(LV)                                                                                   \

@@ -75,6 +75,12 @@ struct cgb_csr {
   std::vector<cgb_csr *> panels;
   int panels_req = 0;    // cgb_csr_set_panels: 0 = automatic (by the size of the gathered vector), 1 = none, P = P panels
   bool panels_ok = true; // false for the library's internal sub-matrices (panels themselves, multi-GPU blocks)
+  // row-pattern dictionary copy (dict.cu, spmv_dict.cuh): explicit format CGB_FMT_DICT
+  uint16_t *dict_ids = nullptr; // pattern of each row
+  int32_t *dict_ptr = nullptr, *dict_off = nullptr;
+  double *dict_val = nullptr;
+  int dict_npat = 0, dict_nent = 0;
+  int grid_dict = 0;
   cgb::Workspace ws;
 };
 
@@ -82,6 +88,8 @@ namespace cgb {
 int csr_plan(cgb_csr *A);
 int csr_build_panels(cgb_csr *A, int P, int sigma); // sell.cu
 void csr_release_panels(cgb_csr *A);
+int csr_build_dict(cgb_csr *A); // dict.cu
+void csr_release_dict(cgb_csr *A);
 int csr_prepare(cgb_csr *A); // before any SpMV-shaped launch: statistics, CGB_FMT_AUTO decision, lazy SELL build
 int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap);
 void workspace_release(cgb_csr *A);

@@ -192,6 +192,13 @@ class Matrix:
     def panels(self) -> int:
         return int(self.ctx.lib.cgb_csr_get_panels(self.h))
 
+    def dict_bytes(self) -> int:
+        """Size of the row-pattern dictionary copy (CGB_FMT_DICT), 0 when not built."""
+        return int(self.ctx.lib.cgb_csr_dict_bytes(self.h))
+
+    def dict_patterns(self) -> int:
+        return int(self.ctx.lib.cgb_csr_dict_patterns(self.h))
+
     def sell_padded(self) -> int:
         return int(self.ctx.lib.cgb_csr_sell_padded(self.h))
 

@@ -31,7 +31,8 @@ enum {
   CGB_ERR_CUDA = 2,    /* CUDA runtime error, see cgb_last_error() */
   CGB_ERR_NCCL = 3,    /* NCCL error / NCCL not loadable */
   CGB_ERR_STATE = 4,   /* missing matrix / right-hand side (src/CG.hpp:266-272) */
-  CGB_ERR_IO = 5       /* Matrix Market file problems */
+  CGB_ERR_IO = 5,      /* Matrix Market file problems */
+  CGB_ERR_UNSUPPORTED = 6 /* the matrix does not fit the requested storage format (CGB_FMT_DICT) */
 };
 
 typedef struct cgb_ctx cgb_ctx;       /* device + stream; replaces acpp::sycl::queue (src/CG.hpp:61,70-77) */
@@ -104,7 +105,17 @@ int64_t cgb_csr_sell_padded(const cgb_csr *A);
  * arrays as they are (TMA-staged tiles); CGB_FMT_AUTO switches to the SELL copy when the row lengths are
  * irregular (tiles that overflow a TMA stage, or a long tail); CGB_FMT_SELL builds the SELL copy on first
  * use (sigma = 32768) unless cgb_csr_build_sell was called with another window. */
-enum { CGB_FMT_AUTO = 0, CGB_FMT_CSR = 1, CGB_FMT_SELL = 2 };
+enum { CGB_FMT_AUTO = 0, CGB_FMT_CSR = 1, CGB_FMT_SELL = 2, CGB_FMT_DICT = 3 };
+/* CGB_FMT_DICT (explicit option, never chosen by CGB_FMT_AUTO): row-pattern dictionary copy.  A matrix from a
+ * constant-coefficient stencil repeats a handful of row patterns (the sequence of (column - row, value) pairs of a
+ * row: 27 for a 7-point Laplacian on a box); with at most 1024 distinct patterns holding at most 3072 entries in
+ * total, the matrix is stored as one 16-bit pattern id per row plus the pattern table: 2 bytes per ROW instead of
+ * CSR's 12 per non-zero.  Lossless (every row is verified against its pattern); row sums keep the CSR entry order,
+ * so results are bit-identical to the one-lane-per-row CSR engines.  cgb_csr_set_format returns CGB_ERR_UNSUPPORTED
+ * (and leaves the format unchanged) when the matrix does not fit.  cgb_csr_dict_bytes: size of the copy (0: not
+ * built); cgb_csr_dict_patterns: distinct row patterns found. */
+int64_t cgb_csr_dict_bytes(const cgb_csr *A);
+int cgb_csr_dict_patterns(const cgb_csr *A);
 int cgb_csr_set_format(cgb_csr *A, int format);
 int cgb_csr_get_format(const cgb_csr *A);
 /* Column panels of the SELL engine: A = [A_0 | ... | A_{P-1}] split by column range, one pass per panel

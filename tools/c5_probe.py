@@ -14,7 +14,9 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
     ctx = S.Context(0)
     t0 = time.time()
-    A = S.Matrix.random_spd(ctx, n)
+    kind = os.environ.get("C5_KIND", "rspd")              # rspd | 3d27 | 3d7 | 2d5 (the argument is the grid size m then)
+    A = S.Matrix.random_spd(ctx, n) if kind == "rspd" else S.Matrix.stencil(ctx, kind, n, n, 0, -1)
+    n = A.N()
     ctx.sync()
     nnz = A.NNZ()
     print(f"generated n={n} nnz={nnz} mean={nnz / n:.2f} in {time.time() - t0:.2f}s", flush=True)
@@ -25,7 +27,7 @@ def main():
     cfgs = os.environ.get("C5_CONFIGS", "csr:0,sell:32768:1,sell:32768:2,sell:32768:3,sell:32768:4,sell:32768:6,sell:32768:8")
     for cfg in cfgs.split(","):
         f = cfg.split(":")
-        fmt, sigma, panels = (L.FMT_SELL if f[0] == "sell" else L.FMT_CSR), int(f[1]), int(f[2]) if len(f) > 2 else 1
+        fmt, sigma, panels = {"sell": L.FMT_SELL, "dict": L.FMT_DICT}.get(f[0], L.FMT_CSR), int(f[1]), int(f[2]) if len(f) > 2 else 1
         A.set_format(L.FMT_CSR)
         if fmt == L.FMT_SELL:
             t0 = time.time()
@@ -34,6 +36,8 @@ def main():
             A.set_format(L.FMT_SELL)
             ctx.sync()
             tb = time.time() - t0
+        if fmt == L.FMT_DICT:
+            A.set_format(L.FMT_DICT)
         for fused in (0,):
             cg = S.CG(ctx, fuse_p_update=fused, time_kernels=1)
             cg.setMatrix(A)
@@ -45,7 +49,7 @@ def main():
             it = st["iterations"]
             rr, xx = cg.residual()
             extra = f" sell_padded={A.sell_padded() / nnz:.3f}x build={tb:.2f}s sigma={sigma} panels={A.panels()}" if fmt == L.FMT_SELL else ""
-            print(f"fmt={'SELL' if fmt == L.FMT_SELL else 'CSR '} fused={fused} it={it} {it / sec:8.1f} it/s {it * B_iter / sec / 1e9:7.1f} GB/s(B_iter) "
+            print(f"fmt={ {L.FMT_SELL: 'SELL', L.FMT_DICT: 'DICT'}.get(fmt, 'CSR ') } fused={fused} it={it} {it / sec:8.1f} it/s {it * B_iter / sec / 1e9:7.1f} GB/s(B_iter) "
                   f"spmv {st['spmv_ms']:.4f} ms true_rel_res={np.sqrt(rr) / (tol / 1e-8):.2e}{extra}", flush=True)
 
 

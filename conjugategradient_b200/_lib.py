@@ -29,7 +29,7 @@ class CgOpts(C.Structure):
     _fields_ = [
         ("loop_mode", C.c_int), ("check_every", C.c_int), ("fuse_p_update", C.c_int),
         ("time_kernels", C.c_int), ("l2_persist_p", C.c_int), ("record_history", C.c_int),
-        ("residual_replace_every", C.c_int), ("reserved", C.c_int * 5),
+        ("residual_replace_every", C.c_int), ("jacobi", C.c_int), ("reserved", C.c_int * 4),
     ]
 
 

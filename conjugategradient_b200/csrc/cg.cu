@@ -36,6 +36,7 @@ struct LoopCfg {
   SpmvLaunch sl;
   int grid_vec;
   int grid_pup;
+  bool jacobi;     // Jacobi-preconditioned variants of the vector kernels
   bool replace;    // residual replacement at the end of every batch
   const double *b; // right-hand side (replacement only)
 };
@@ -49,7 +50,8 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
     return timed ? cudaEventRecordWithFlags(w.ev[i], s, cudaEventRecordExternal) : cudaSuccess;
   };
   CGB_CUDA(mark(0));
-  if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
+  if (c.jacobi) cg_pupdate_jacobi_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.dinv, w.p0, x, w.st);
+  else if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_CUDA(mark(1));
   launch_panel_partials(A, c.sl, s, w.p0, w.Ap, w.st); // column panels 0 .. P-2: Ap accumulates
   dispatch_lanes(c.sl.lanes, c.sl.eng, [&](auto Lc, auto Tc) {
@@ -63,8 +65,9 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
                     (double *)nullptr);
   });
   CGB_CUDA(mark(2));
-  cg_update_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, (const double *)nullptr,
-                                                 (double *)nullptr);
+  if (c.jacobi) cg_update_jacobi_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.dinv, w.st, w.partials, w.hist);
+  else cg_update_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, (const double *)nullptr,
+                                                      (double *)nullptr);
   CGB_CUDA(mark(3));
   CGB_CUDA(cudaGetLastError());
   return CGB_OK;
@@ -79,6 +82,7 @@ static int enqueue_replacement(cgb_csr *A, double *x, const LoopCfg &c, cudaStre
     launch_kernel(cg_replace_kernel<decltype(Lc)::value, decltype(Tc)::value>, c.sl, s, csr_view_final(A, w.r),
                   (const double *)x, c.b, w.r, w.st, w.partials);
   });
+  if (c.jacobi) cg_rho_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.dinv, w.st, w.partials, 1);
   CGB_CUDA(cudaGetLastError());
   return CGB_OK;
 }
@@ -168,10 +172,11 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   // system is small enough that latency rules (CGB_PERSISTENT_MAX_N rows); it serves CSR rows only.
   int64_t persistent_max_n = 131072; // measured cross-over on B200: 2D 5-pt 256^2 still wins (89k vs 77k it/s), 512^2 loses
   if (const char *e = getenv("CGB_PERSISTENT_MAX_N")) persistent_max_n = atoll(e);
-  const bool can_persist = !replace && ctx->coop_ok && (csr_engine(A) == kEngTma || csr_engine(A) == kEngVec) && !o.time_kernels;
+  const bool jacobi = o.jacobi != 0;
+  const bool can_persist = !replace && !jacobi && ctx->coop_ok && (csr_engine(A) == kEngTma || csr_engine(A) == kEngVec) && !o.time_kernels;
   const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
   if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
-  const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
+  const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0 && !jacobi) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
   // L2 window: explicit option, or CGB_L2_WINDOW=1/0; only meaningful without the fused p-update (p ping-pongs there)
@@ -185,7 +190,24 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
       l2w = false;
     }
   }
-  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, replace, d_b};
+  if (jacobi && !w.dinv) { // 1 / diag(A), once per matrix
+    int *d_bad = nullptr;
+    CGB_CUDA(cudaMalloc(&w.dinv, sizeof(double) * (size_t)n));
+    CGB_CUDA(cudaMalloc(&d_bad, sizeof(int)));
+    CGB_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), s));
+    diag_inv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, A->rowptr, A->cols, A->vals, w.dinv, d_bad);
+    int bad = 0;
+    cudaError_t e = cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_bad);
+    if (e != cudaSuccess || bad) {
+      cudaFree(w.dinv);
+      w.dinv = nullptr;
+      if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "diag_inv_kernel: %s", cudaGetErrorString(e));
+      return fail(CGB_ERR_UNSUPPORTED, "Jacobi preconditioner: a row has no non-zero diagonal entry");
+    }
+  }
+  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, jacobi, replace, d_b};
   if (l2w) {
     cudaStreamAttrValue v;
     memset(&v, 0, sizeof(v));
@@ -226,6 +248,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   init.max_iter = max_iter;
   init.record_history = o.record_history ? 1 : 0;
   init.hist_cap = w.hist_cap;
+  init.precond = jacobi ? 1 : 0;
   init.done = 1; // K0 arms the loop; until then nothing may run
   w.h_st[0] = init;
   CGB_CUDA(cudaMemcpyAsync(w.st, &w.h_st[0], sizeof(CgState), cudaMemcpyHostToDevice, s));
@@ -237,10 +260,12 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     launch_kernel(cg_init_kernel<decltype(Lc)::value, decltype(Tc)::value>, cfg.sl, s, csr_view_final(A, w.r),
                   (const double *)d_x, d_b, w.r, w.st, w.partials, w.hist);
   });
+  if (jacobi) cg_rho_kernel<<<cfg.grid_vec, kBlock, 0, s>>>(n, w.r, w.dinv, w.st, w.partials, 0);
   CGB_CUDA(cudaGetLastError());
-  int64_t launches = 1 + extra;
+  int64_t launches = 1 + extra + (jacobi ? 1 : 0);
 
   const int per_iter = (fused ? 2 : 3) + (int)extra;
+  const int per_replace = 2 + (int)extra + (jacobi ? 1 : 0);
   double t_p = 0, t_s = 0, t_u = 0;
   int64_t samples = 0;
   if (persistent) {
@@ -272,7 +297,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
                          (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.eng << 2) ^
-                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)replace << 5) ^ ((uint64_t)csr_panels(A) << 48);
+                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)replace << 5) ^ ((uint64_t)jacobi << 6) ^ ((uint64_t)csr_panels(A) << 48);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an
@@ -295,7 +320,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
       for (int i = 0; i < batch; i++) CGB_TRY(enqueue_iteration(A, d_x, cfg, s, cfg.time_kernels && i == 0));
       if (replace) CGB_TRY(enqueue_replacement(A, d_x, cfg, s));
     }
-    launches += (int64_t)batch * per_iter + (replace ? 2 + extra : 0);
+    launches += (int64_t)batch * per_iter + (replace ? per_replace : 0);
     issued += batch;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[slot], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaEventRecord(polled[slot], s));

@@ -188,7 +188,7 @@ __global__ void CGB_BOUNDS(ENG) cg_spmv_kernel(CsrView A, const double *__restri
         *local_out = pAp; // multi-GPU: all-reduced before K2 forms alpha
       } else {
         st->pAp = pAp;
-        st->alpha = st->rr / pAp; // src/CG.hpp:385-386
+        st->alpha = (st->precond ? st->rho : st->rr) / pAp; // src/CG.hpp:385-386 (rho = r.z with Jacobi)
       }
     }
   }
@@ -260,6 +260,85 @@ static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, dou
       }
     }
   }
+}
+
+// ---- Jacobi-preconditioned variants (optional; not in the reference: SURVEY.md §8f row 4) --------------
+// z = D^-1 r is never stored: it is formed on the fly from dinv = 1 / diag(A) where it is needed.
+//   p-update   p = z + beta p           (and the deferred x update, as in cg_pupdate_kernel)
+//   r-update   r -= alpha Ap ; rr' = r.r (stop rule, unchanged) ; rho' = r.z ; beta = rho'/rho
+static __global__ void __launch_bounds__(kBlock) cg_pupdate_jacobi_kernel(int64_t n, const double *__restrict__ r,
+                                                                    const double *__restrict__ dinv, double *__restrict__ p,
+                                                                    double *__restrict__ x, const CgState *st) {
+  if (!cg_active(st)) return;
+  const double beta = st->beta, alpha = st->alpha;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double po = p[i];
+    x[i] = fma(alpha, po, x[i]);
+    p[i] = fma(beta, po, dinv[i] * r[i]);
+  }
+}
+
+static __global__ void __launch_bounds__(kBlock) cg_update_jacobi_kernel(int64_t n, double *__restrict__ r,
+                                                                   const double *__restrict__ Ap,
+                                                                   const double *__restrict__ dinv, CgState *st,
+                                                                   double *partials, double *hist) {
+  if (!cg_active(st)) return;
+  __shared__ double red[32];
+  const double alpha = st->alpha;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double a_rr = 0.0, a_rz = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double rv = fma(-alpha, Ap[i], r[i]);
+    r[i] = rv;
+    a_rr = fma(rv, rv, a_rr);
+    a_rz = fma(dinv[i] * rv, rv, a_rz);
+  }
+  a_rr = block_sum(a_rr, red);
+  a_rz = block_sum(a_rz, red);
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = a_rr;
+    partials[kMaxPartials + blockIdx.x] = a_rz;
+  }
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rr_new = reduce_partials(partials, gridDim.x, red);
+    const double rho_new = reduce_partials(partials + kMaxPartials, gridDim.x, red);
+    if (threadIdx.x == 0) {
+      const double rho = st->rho;
+      cg_advance_state(st, rr_new, hist); // stop rule on the un-preconditioned residual, as the reference's
+      st->beta = rho_new / rho;
+      st->rho = rho_new;
+    }
+  }
+}
+
+// rho = r.z from the current r (after K0 and after a residual replacement)
+static __global__ void __launch_bounds__(kBlock) cg_rho_kernel(int64_t n, const double *__restrict__ r,
+                                                         const double *__restrict__ dinv, CgState *st, double *partials,
+                                                         int gated) {
+  if (gated && !cg_active(st)) return;
+  __shared__ double red[32];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  double a = 0.0;
+  for (int64_t i = tid; i < n; i += nthr) a = fma(dinv[i] * r[i], r[i], a);
+  a = block_sum(a, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = a;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rho = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) st->rho = rho;
+  }
+}
+
+// dinv[i] = 1 / A_ii; *bad = 1 when a row has no (or a zero) diagonal entry
+static __global__ void diag_inv_kernel(int64_t n, const int *__restrict__ rowptr, const int *__restrict__ cols,
+                                       const double *__restrict__ vals, double *__restrict__ dinv, int *bad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double d = 0.0;
+  for (int j = rowptr[i], e = rowptr[i + 1]; j < e; j++)
+    if (cols[j] == i) d += vals[j];
+  if (d == 0.0) atomicExch(bad, 1);
+  dinv[i] = 1.0 / d;
 }
 
 // ---- KX -------------------------------------------------------------------------------------

@@ -58,7 +58,8 @@ struct CgState {
   int record_history;
   long long hist_cap;
   int comm_error; // multi-GPU: a peer wait timed out (the loop is stopped, the host reports it)
-  int pad_;
+  int precond;    // 1: Jacobi-preconditioned loop (rho = r.z drives alpha and beta, rr only the stop rule)
+  double rho;     // r.z of the current iteration (precond only)
 };
 
 struct Workspace;

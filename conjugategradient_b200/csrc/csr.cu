@@ -142,6 +142,7 @@ void workspace_release(cgb_csr *A) {
   cudaFree(w.p0);
   cudaFree(w.p1);
   cudaFree(w.Ap);
+  cudaFree(w.dinv);
   cudaFree(w.st);
   cudaFree(w.partials);
   cudaFree(w.hist);

@@ -16,6 +16,7 @@ struct Workspace {
   double *p0 = nullptr; // p (unfused) / ping
   double *p1 = nullptr; // pong (fused p-update only, lazily allocated)
   double *Ap = nullptr;
+  double *dinv = nullptr; // 1 / diag(A), built on the first Jacobi-preconditioned solve
   CgState *st = nullptr;
   double *partials = nullptr; // kMaxPartials * 2
   double *hist = nullptr;

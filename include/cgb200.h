@@ -184,7 +184,11 @@ typedef struct cgb_cg_opts {
                            reference's recurrence does at tight tolerances; one extra
                            SpMV per k iterations; single-GPU graph / stepwise loops.  0 (default): classical
                            recurrence, as the reference */
-  int reserved[5];
+  int jacobi;           /* 1: Jacobi-preconditioned CG (z = D^-1 r formed on the fly from 1/diag(A); alpha and beta
+                           from r.z; the stop rule stays on |r|).  A different algorithm from the reference's:
+                           iteration counts are not comparable with it.  Single-GPU graph / stepwise loops.
+                           CGB_ERR_UNSUPPORTED when a row has no non-zero diagonal entry.  0 (default): plain CG */
+  int reserved[4];
 } cgb_cg_opts;
 
 typedef struct cgb_cg_stats {

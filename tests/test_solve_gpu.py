@@ -239,3 +239,77 @@ def test_residual_replacement_keeps_the_stop_rule_honest(ctx, port, fused):
     assert st2["converged"] == 1 and abs(st2["iterations"] - o["iterations"]) <= 20
     assert rel_err(rep.extract(), o["x"]) <= 1e-8
     assert np.sqrt(rep.residual()[0]) <= 1.01 * tol + 1e-9 * nb
+
+
+def _pcg_jacobi_numpy(v, c, r, b, tol, max_iter):
+    """Jacobi-preconditioned CG with the reference's stop rule (absolute tolerance on |r|, tested one trip late,
+    src/CG.hpp:396-404) — the plain-NumPy statement of what opts.jacobi runs."""
+    import scipy.sparse as sp
+    n = r.size - 1
+    A = sp.csr_matrix((v, c, r), shape=(n, n))
+    dinv = 1.0 / A.diagonal()
+    x = np.zeros(n)
+    res = b.copy()
+    z = dinv * res
+    p = np.zeros(n)
+    rr, rho, beta, it = float(res @ res), float(res @ z), 0.0, 0
+    while it < max_iter:
+        p = z + beta * p
+        Ap = A @ p
+        alpha = rho / float(p @ Ap)
+        x += alpha * p
+        res -= alpha * Ap
+        z = dinv * res
+        rr_new, rho_new = float(res @ res), float(res @ z)
+        stop = np.sqrt(rr) <= tol
+        beta, rho, rr = rho_new / rho, rho_new, rr_new
+        it += 1
+        if stop:
+            break
+    return x, it
+
+
+def test_jacobi_preconditioner_option(ctx):
+    """Additive option: a badly scaled SPD system, D^1/2 A D^1/2 with D spanning six decades,
+    needs far fewer trips with z = diag(A)^-1 r; trips and x agree with the NumPy statement of the same algorithm."""
+    import scipy.sparse as sp
+    v, c, r = G.poisson3d_7pt(24)
+    n = r.size - 1
+    rng = np.random.default_rng(4)
+    d = 10.0 ** rng.uniform(-3, 3, n)
+    A = sp.diags(np.sqrt(d)) @ sp.csr_matrix((v, c, r), shape=(n, n)) @ sp.diags(np.sqrt(d))
+    A = A.tocsr()
+    A.sort_indices()
+    v2, c2, r2 = A.data.copy(), A.indices.astype(np.int32), A.indptr.astype(np.int32)
+    b = G.default_rhs(n)
+    tol = 1e-9 * np.linalg.norm(b)
+    xr, itr = _pcg_jacobi_numpy(v2, c2, r2, b, tol, n + 1)
+    pcg = S.CG(ctx, jacobi=1)
+    pcg.setMatrix(v2, c2, r2)
+    pcg.setTarget(b)
+    st = pcg.solve(tol)
+    assert st["converged"] == 1 and abs(st["iterations"] - itr) <= max(1, round(0.02 * itr))
+    assert rel_err(pcg.extract(), xr) <= 1e-8
+    assert np.sqrt(pcg.residual()[0]) <= 10 * tol
+    plain = S.CG(ctx)
+    plain.setMatrix(v2, c2, r2)
+    plain.setTarget(b)
+    st0 = plain.solve(tol, max_iter=20 * st["iterations"])
+    assert st0["iterations"] > 5 * st["iterations"]                  # what the preconditioner buys on this system
+    # with residual replacement on top, and deterministic
+    both = S.CG(ctx, jacobi=1, residual_replace_every=16)
+    both.setMatrix(v2, c2, r2)
+    both.setTarget(b)
+    st2 = both.solve(tol)
+    assert st2["converged"] == 1 and abs(st2["iterations"] - itr) <= 16 and rel_err(both.extract(), xr) <= 1e-8
+    x1 = pcg.extract().copy()
+    pcg.x = None
+    pcg.solve(tol)
+    assert np.array_equal(pcg.extract(), x1)
+    # a matrix without a diagonal is refused
+    bad = S.CG(ctx, jacobi=1)
+    bad.setMatrix(np.array([1.0, 1.0]), np.array([1, 0], np.int32), np.array([0, 1, 2], np.int32))
+    bad.setTarget(np.ones(2))
+    with pytest.raises(L.CgbError) as e:
+        bad.solve(1e-8)
+    assert e.value.code == L.CGB_ERR_UNSUPPORTED

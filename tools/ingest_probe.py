@@ -1,7 +1,8 @@
 """Matrix Market ingest probe: the same file through
-  (a) the reference's own read_file (oracle/_ref, unmodified test/mm_reader.cpp), when built,
-  (b) cgb_mm_read with one host thread and with all of them (host CSR),
-  (c) cgb_csr_from_mm_file (parallel parse + CSR assembled on the GPU), when a GPU is present.
+  (a) cgb_mm_read with one host thread and with all of them (host CSR),
+  (b) cgb_csr_from_mm_file (parallel parse + CSR assembled on the GPU), when a GPU is present.
+The reference's own read_file on the same kind of file is timed by tests/test_reader.py::test_reader_vs_reference_speed
+(the oracle is test infrastructure and is not imported from here).
 python tools/ingest_probe.py [m]      3D 7-point Poisson m^3 (default 128 = BASELINE config C2)"""
 import os
 import sys
@@ -32,11 +33,6 @@ def main():
             ts.append(time.time() - t0)
         return min(ts), out
 
-    import oracle
-    if oracle.have_ref("serial"):
-        t, out = best(lambda: oracle.Ref("serial").mm_read(path), reps=1)
-        assert all(np.array_equal(a, b) for a, b in zip(out, (v, c, r)))
-        print(f"reference read_file (test/mm_reader.cpp, 1 thread): {t:.2f} s", flush=True)
     for th in (1, os.cpu_count() or 1):
         os.environ["CGB_MM_THREADS"] = str(th)
         t, out = best(lambda: S.mm_read(path))

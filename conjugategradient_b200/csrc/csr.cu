@@ -52,6 +52,7 @@ int csr_plan(cgb_csr *A) {
   // TMA engine: a tile of 256 / L rows should carry about 7 * 256 non-zeros
   int lt = 1;
   while (lt < 32 && (double)lt * 7.0 < mean) lt <<= 1;
+  if (const char *e = getenv("CGB_TMA_LANES")) lt = atoi(e) > 0 ? atoi(e) : lt; // A/B measurements
   A->lanes_tma = lt;
   const int tile_rows = kTmaConsumers / lt;
   const size_t smem = tma_smem_bytes(tile_rows) + 1024;

@@ -66,7 +66,8 @@ __device__ __forceinline__ void spmv_rows(const CsrView &A, const G &g, const E 
 }
 // min-CTAs 0 = unspecified: an explicit 1 lets ptxas grow the TMA kernel from 54 to 90 registers (2 CTAs per SM
 // instead of 3: C3 894 -> 720 it/s)
-#define CGB_BOUNDS(ENG) __launch_bounds__((ENG) == kEngTma ? kTmaThreads : kBlock, (ENG) == kEngSell ? kSellMinCtas : 0)
+#define CGB_BOUNDS(ENG) \
+  __launch_bounds__((ENG) == kEngTma ? kTmaThreads : kBlock, (ENG) == kEngSell ? kSellMinCtas : (ENG) == kEngDict ? kDictMinCtas : 0)
 
 __device__ __forceinline__ bool cg_active(const CgState *st) {
   // reference: do { ... } while (counter++ < N && !*is_done)   (src/CG.hpp:436)

@@ -102,8 +102,8 @@ __global__ void dict_assign_kernel(int64_t n, const int *__restrict__ rowptr, co
   bool ok = hs[lo] == h;
   const int p = pid_of[lo];
   if (ok) {
-    const int b = rowptr[row], l = rowptr[row + 1] - b, pb = ptr[p];
-    ok = l == ptr[p + 1] - pb;
+    const int b = rowptr[row], l = rowptr[row + 1] - b, pb = ptr[p] & 0xffff;
+    ok = l == ptr[p] >> 16;
     for (int k = 0; ok && k < l; k++)
       ok = (int)((int64_t)cols[b + k] - row) == off[pb + k] &&
            __double_as_longlong(vals[b + k]) == __double_as_longlong(val[pb + k]);
@@ -184,16 +184,22 @@ int csr_build_dict(cgb_csr *A) {
   CGB_CUDA(cudaMemcpyAsync(off_st.data(), d_off_st.p, sizeof(int) * off_st.size(), cudaMemcpyDeviceToHost, s));
   CGB_CUDA(cudaMemcpyAsync(val_st.data(), d_val_st.p, sizeof(double) * val_st.size(), cudaMemcpyDeviceToHost, s));
   CGB_CUDA(cudaStreamSynchronize(s));
+  // device table: header = first entry | length << 16, patterns padded to kDictAlign entries (spmv_dict.cuh)
   std::vector<int> ptr(npat + 1, 0), off;
   std::vector<double> val;
   for (int p = 0; p < npat; p++) {
-    ptr[p + 1] = ptr[p] + len[p];
+    if (off.size() > 0xffff) break; // caught by the size check below
+    ptr[p] = (int)off.size() | len[p] << 16;
     for (int k = 0; k < len[p]; k++) {
       off.push_back(off_st[(size_t)p * kDictMaxRow + k]);
       val.push_back(val_st[(size_t)p * kDictMaxRow + k]);
     }
+    while (off.size() % kDictAlign) {
+      off.push_back(0);
+      val.push_back(0.0);
+    }
   }
-  const int nent = ptr[npat];
+  const int nent = (int)off.size();
   if (nent > kDictMaxEntries)
     return fail(CGB_ERR_UNSUPPORTED, "row-pattern dictionary: patterns hold %d entries (limit %d)", nent, kDictMaxEntries);
   // lookup arrays sorted by hash

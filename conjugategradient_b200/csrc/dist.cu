@@ -392,6 +392,11 @@ __global__ void __launch_bounds__(kBlock) peer_halo_kernel(int64_t nh, const int
 struct GatherCg { // coherent at L2: the halo buffer is written by peers until the flags are up
   const double *x;
   __device__ __forceinline__ double operator()(int c) const { return __ldcg(x + c); }
+  struct At {
+    const double *xr;
+    __device__ __forceinline__ double operator()(int off) const { return __ldcg(xr + off); }
+  };
+  __device__ __forceinline__ At at(int64_t row) const { return At{x + row}; }
 };
 struct EpiHaloAdd { // y[rows[k]] += s ; acc0 += p[rows[k]] * s
   double *y;

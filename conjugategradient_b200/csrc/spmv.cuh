@@ -16,6 +16,16 @@ namespace cgb {
 struct GatherPlain {
   const double *x;
   __device__ __forceinline__ double operator()(int c) const { return __ldg(x + c); }
+  // gathers relative to one row (dictionary engine): the row's address is formed once
+  struct At {
+    const double *xr;
+    __device__ __forceinline__ double operator()(int off) const { return __ldg(xr + off); }
+  };
+  __device__ __forceinline__ At at(int64_t row) const {
+    const double *xr = x + row;
+    asm("" : "+l"(xr)); // keep (row address) + offset: one multiply-add per gather instead of a 64-bit add and a scale
+    return At{xr};
+  }
 };
 // p = r + beta * p_old formed on the fly (fused p-update); same rounding as the epilogue's p_new.
 struct GatherFusedP {
@@ -23,6 +33,16 @@ struct GatherFusedP {
   const double *p_old;
   double beta;
   __device__ __forceinline__ double operator()(int c) const { return fma(beta, __ldg(p_old + c), __ldg(r + c)); }
+  struct At {
+    const double *rr, *pr;
+    double beta;
+    __device__ __forceinline__ double operator()(int off) const { return fma(beta, __ldg(pr + off), __ldg(rr + off)); }
+  };
+  __device__ __forceinline__ At at(int64_t row) const {
+    const double *rr = r + row, *pr = p_old + row;
+    asm("" : "+l"(rr), "+l"(pr));
+    return At{rr, pr, beta};
+  }
 };
 
 // ---- per-row epilogues: row(i, sum) consumes the finished row sum; acc0/acc1 are the thread's

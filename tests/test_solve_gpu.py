@@ -208,6 +208,47 @@ def test_full_size_properties_C2(ctx):
     assert rel_err(cg2.extract(), 2 * x1) <= 1e-12
 
 
+def test_full_size_properties_C4(ctx):
+    """BASELINE config C4 (3D 7-pt 512^3, n = 134,217,728, the configuration the metric is quoted on), generated on
+    the device; properties that need no oracle run of that size: a checksum of the operator, symmetry, the engines
+    agreeing bit for bit, and the solve reaching the true residual in the trip count the bench reports."""
+    m = 512
+    A = S.Matrix.stencil(ctx, "3d7", m)
+    n = A.N()
+    assert n == m ** 3 and A.NNZ() == G.stencil_nnz("3d7", m) == 937951232
+    ops = S.VectorOperations(ctx)
+    ops.setVectorSize(n)
+    ones, y = S.Vector(ctx, np.ones(n)), S.Vector(ctx, n=n)
+    ops.spmv(A, ones, y)
+    rowsum = y.download()                                 # 6 - (number of neighbours): 0 inside, >0 on the faces
+    assert rowsum.min() == 0.0 and rowsum.max() == 3.0 and rowsum.sum() == 6.0 * m * m
+    rng = np.random.default_rng(5)
+    u, w = rng.standard_normal(n), rng.standard_normal(n)
+    U, W, AU, AW = S.Vector(ctx, u), S.Vector(ctx, w), S.Vector(ctx, n=n), y
+    ops.spmv(A, U, AU)
+    ops.spmv(A, W, AW)
+    au = AU.download()
+    lhs, rhs = float(w @ au), float(u @ AW.download())
+    assert abs(lhs - rhs) <= 1e-10 * (np.linalg.norm(w) * np.linalg.norm(au))          # w.(A u) == u.(A w)
+    A.set_format(L.FMT_DICT)                              # same product through the row-pattern dictionary
+    assert A.dict_patterns() == 27
+    ops.spmv(A, U, AW)
+    assert np.array_equal(AW.download(), au)
+    A.set_format(L.FMT_CSR)
+    del rowsum, u, w, au
+    for v in (ones, U, W, AU):
+        v.free()
+    b = G.default_rhs(n)
+    nb = float(np.sqrt(n * (n + 1) * (2 * n + 1) / 6.0))
+    cg = S.CG(ctx)
+    cg.setMatrix(A)
+    cg.setTarget(b)
+    st = cg.solve(1e-8 * nb)
+    assert st["converged"] == 1 and 1700 <= st["iterations"] <= 1900              # 1798 on every run so far
+    rr, xx = cg.residual()
+    assert np.sqrt(rr) / nb <= 2e-8
+
+
 @pytest.mark.parametrize("fused", [0, 1])
 def test_residual_replacement_keeps_the_stop_rule_honest(ctx, port, fused):
     """Additive option (not in the reference): at a tolerance below what fp64 can reach, the reference's recurrence

@@ -38,7 +38,7 @@ def main():
             tb = time.time() - t0
         if fmt == L.FMT_DICT:
             A.set_format(L.FMT_DICT)
-        for fused in (0,):
+        for fused in [int(v) for v in os.environ.get("C5_FUSED", "0").split(",")]:
             cg = S.CG(ctx, fuse_p_update=fused, time_kernels=1)
             cg.setMatrix(A)
             cg.setTarget(b)

@@ -272,6 +272,8 @@ def run_ours(args, kind, m, rel):
     dh = None
     if world > 1:
         import torch
+        if os.environ.get("CGB_BENCH_FORMAT", "") == "dict":  # debug: the opt-in storage format on every rank's block
+            A.set_format(L.FMT_DICT)
         idbuf = (C.c_ubyte * L.NCCL_ID_BYTES)()
         if rank == 0:
             L.check(lib.cgb_nccl_unique_id(idbuf))
@@ -483,7 +485,7 @@ def run_ours(args, kind, m, rel):
                                   iterations_per_solve=last["iterations"], true_rel_residual=true_rel,
                                   loop=("one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT
                                         else "CUDA graph batches of %d iterations, device-side stop flag" % args.check_every),
-                                  engine="SELL-32-sigma" if last["format"] == L.FMT_SELL else "CSR TMA-staged",
+                                  engine={L.FMT_SELL: "SELL-32-sigma", L.FMT_DICT: "row-pattern dictionary (explicit option)"}.get(last["format"], "CSR TMA-staged"),
                                   transport=(os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None)),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "achieved_GBps_B_iter": iters * b_iter(n, nnz) / (ms_total * 1e6),

@@ -243,6 +243,12 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   CGB_TRY(cgb_csr_from_device(ctx, nh, nnz_halo, vals_halo, cols_halo, rowptr_halo, 1, &d->Ahalo));
   d->Aloc->panels_ok = d->Ahalo->panels_ok = false; // the distributed loop launches one kernel per block itself
   d->Ahalo->n_cols = H;
+  // An explicit storage format on the caller's block carries over to its local part, which holds nearly all the
+  // entries (the halo part keeps the automatic choice).  A block that does not fit the format stays as it is.
+  if (A->format != CGB_FMT_AUTO) {
+    const int rc = cgb_csr_set_format(d->Aloc, A->format);
+    if (rc != CGB_OK && rc != CGB_ERR_UNSUPPORTED) return rc;
+  }
 
   // who sends what: receive counts per owner, all-gathered into a matrix
   std::vector<int32_t> h_recv;
@@ -498,7 +504,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     stats->solve_ms = ms;
     stats->kernel_launches = launches;
     stats->loop_mode = use_graph ? CGB_LOOP_GRAPH : CGB_LOOP_STEPWISE;
-    stats->format = csr_engine(A) == kEngSell ? CGB_FMT_SELL : CGB_FMT_CSR;
+    { const int eng = csr_engine(A); stats->format = eng == kEngSell ? CGB_FMT_SELL : eng == kEngDict ? CGB_FMT_DICT : CGB_FMT_CSR; }
   }
   return CGB_OK;
 }

@@ -11,6 +11,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
+from conjugategradient_b200 import _lib as L  # noqa: E402
 from conjugategradient_b200 import generators as G  # noqa: E402
 from conjugategradient_b200 import solver as S  # noqa: E402
 
@@ -38,6 +39,12 @@ def main():
         lo, hi = int(starts[rank]), int(starts[rank + 1])
         lv, lc, lr = S.local_block(v, c, r, lo, hi)
         A = S.Matrix(ctx, lv, lc, lr)
+        want = os.environ.get("CGB_TEST_FORMAT", "")
+        if want == "dict":                       # explicit storage option, inherited by the rank's local block
+            try:
+                A.set_format(L.FMT_DICT)
+            except RuntimeError:
+                want = ""                        # random SPD: as many patterns as rows, stays CSR / SELL
         if dcg is None:
             dcg = S.DistCG(ctx, rank, world, nccl_id, starts, A)
         else:
@@ -57,6 +64,7 @@ def main():
             ok_it = abs(st["iterations"] - o["iterations"]) <= max(1, round(slack * o["iterations"]))
             true_rr = float(np.sum((b - oracle.Port().spmv(v, c, r, x)) ** 2))
             ok = ok_it and err <= 1e-10 and st["converged"] == 1 and abs(rr - true_rr) <= (1e-13 / rel) * true_rr + 1e-30
+            ok = ok and (want != "dict" or st["format"] == L.FMT_DICT)
             print(f"{'DIST_OK' if ok else 'DIST_FAIL'} {name} world={world} it={st['iterations']} oracle_it={o['iterations']} "
                   f"err={err:.2e} halo={dcg.halo_count()} rr={rr:.3e} true_rr={true_rr:.3e}", flush=True)
         dist.barrier()

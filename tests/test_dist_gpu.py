@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("variant", ["default", "halo_engine", "nccl"])
+@pytest.mark.parametrize("variant", ["default", "halo_engine", "nccl", "dict"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_dist_solve_matches_oracle(world, variant):
     if L.load().cgb_device_count() < world:
@@ -21,6 +21,8 @@ def test_dist_solve_matches_oracle(world, variant):
         env["CGB_HALO_ENGINE_MIN"] = "1"      # A_halo through the regular row engines even for these small cases
     if variant == "nccl":
         env["CGB_DIST_TRANSPORT"] = "nccl"    # the fallback transport stays correct
+    if variant == "dict":
+        env["CGB_TEST_FORMAT"] = "dict"       # row-pattern dictionary on every rank's local block
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(29610 + world), os.path.join(ROOT, "tests", "dist_worker.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)

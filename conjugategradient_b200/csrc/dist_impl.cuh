@@ -172,8 +172,10 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   CGB_TRY(dev_alloc(b_tmp, tmp_bytes));
 
   // A_loc row offsets
+  DevBuf g_rl, g_rh, g_cl, g_vl, g_ch, g_vh; // own the new arrays until the two handles below take them over
   int32_t *rowptr_loc = nullptr;
   CGB_CUDA(cudaMalloc(&rowptr_loc, sizeof(int32_t) * (size_t)(n + 1) + 64));
+  g_rl.p = rowptr_loc;
   CGB_CUDA(cudaMemsetAsync(rowptr_loc, 0, sizeof(int32_t), s));
   int nnz_loc = 0, nh = 0, nnz_halo = 0;
   if (n > 0) {
@@ -193,6 +195,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   // A_halo row offsets: compact the non-zero remote counts (row order), then scan
   int32_t *rowptr_halo = nullptr;
   CGB_CUDA(cudaMalloc(&rowptr_halo, sizeof(int32_t) * (size_t)(nh + 1) + 64));
+  g_rh.p = rowptr_halo;
   CGB_CUDA(cudaMemsetAsync(rowptr_halo, 0, sizeof(int32_t), s));
   if (nh > 0) {
     t = tmp_bytes;
@@ -230,9 +233,13 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   int32_t *cols_loc = nullptr, *cols_halo = nullptr;
   double *vals_loc = nullptr, *vals_halo = nullptr;
   CGB_CUDA(cudaMalloc(&cols_loc, sizeof(int32_t) * (size_t)nnz_loc + 64));
+  g_cl.p = cols_loc;
   CGB_CUDA(cudaMalloc(&vals_loc, sizeof(double) * (size_t)nnz_loc + 64));
+  g_vl.p = vals_loc;
   CGB_CUDA(cudaMalloc(&cols_halo, sizeof(int32_t) * (size_t)nnz_halo + 64));
+  g_ch.p = cols_halo;
   CGB_CUDA(cudaMalloc(&vals_halo, sizeof(double) * (size_t)nnz_halo + 64));
+  g_vh.p = vals_halo;
   CGB_CUDA(cudaMalloc(&d->halo_rows, sizeof(int32_t) * (size_t)(nh + 1)));
   if (n > 0) {
     split_fill_kernel<<<gb, tb, 0, s>>>(n, A->rowptr, A->cols, A->vals, lo, hi, rowptr_loc, cols_loc, vals_loc, cnt_rem,
@@ -240,7 +247,9 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
     CGB_CUDA(cudaGetLastError());
   }
   CGB_TRY(cgb_csr_from_device(ctx, n, nnz_loc, vals_loc, cols_loc, rowptr_loc, 1, &d->Aloc));
+  g_rl.p = g_cl.p = g_vl.p = nullptr;
   CGB_TRY(cgb_csr_from_device(ctx, nh, nnz_halo, vals_halo, cols_halo, rowptr_halo, 1, &d->Ahalo));
+  g_rh.p = g_ch.p = g_vh.p = nullptr;
   d->Aloc->panels_ok = d->Ahalo->panels_ok = false; // the distributed loop launches one kernel per block itself
   d->Ahalo->n_cols = H;
   // An explicit storage format on the caller's block carries over to its local part, which holds nearly all the

@@ -354,15 +354,18 @@ def run_ours(args, kind, m, rel):
     # ---- roofline of the dominant kernel (SpMV + p.Ap), timed live with CUDA events ----------------
     peak, peak_src = measured_peak()
     roof = None
-    if last["loop_mode"] == L.LOOP_PERSISTENT:
-        # one cooperative kernel runs the whole solve: its launch = all iterations (bandwidth fraction is not meaningful
+    if last["loop_mode"] in (L.LOOP_PERSISTENT, L.LOOP_CLUSTER):
+        # one kernel runs the whole solve: its launch = all iterations (bandwidth fraction is not meaningful
         # at this size -- 2.5 MB per iteration lives in L2; the figure of merit is microseconds per iteration)
         by = last["iterations"] * b_iter(n, nnz)
         ms1 = ms_total / args.steps
-        roof = {"bound": "hbm", "kernel": "cg_persistent_kernel (whole CG loop, cooperative launch)", "achieved": by / (ms1 * 1e6),
+        kname = ("cg_cluster_kernel (whole CG loop in one 16-CTA cluster, matrix and vectors in distributed shared memory)"
+                 if last["loop_mode"] == L.LOOP_CLUSTER else "cg_persistent_kernel (whole CG loop, cooperative launch)")
+        roof = {"bound": "hbm", "kernel": kname, "achieved": by / (ms1 * 1e6),
                 "peak": peak, "unit": "GB/s", "frac": by / (ms1 * 1e6) / peak, "peak_source": peak_src, "traffic": None,
                 "bytes_per_launch": by, "ms_per_launch": ms1, "share_of_iteration": 1.0,
-                "us_per_iteration": 1e3 * ms_total / max(iters, 1), "regime": "latency-bound (working set in L2)"}
+                "us_per_iteration": 1e3 * ms_total / max(iters, 1), "regime": ("latency-bound (working set in shared memory; no HBM traffic inside the loop)"
+                           if last["loop_mode"] == L.LOOP_CLUSTER else "latency-bound (working set in L2)")}
     spmv = [o["spmv_ms"] for o in outs if o["timed_samples"] > 0]
     if spmv:
         k1_bytes = 12 * nnz + 4 * (n + 1) + 16 * n  # vals + cols + rowptr + p read + Ap write
@@ -483,7 +486,8 @@ def run_ours(args, kind, m, rel):
             "config": config_dict(args.workload, kind, m, n, nnz, rel, f"{world}xB200",
                                   parallelism=f"row-partitioned x{world}" if world > 1 else "single GPU",
                                   iterations_per_solve=last["iterations"], true_rel_residual=true_rel,
-                                  loop=("one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT
+                                  loop=("one thread-block cluster per solve (cluster barriers, distributed shared memory)" if last["loop_mode"] == L.LOOP_CLUSTER
+                                        else "one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT
                                         else "CUDA graph batches of %d iterations, device-side stop flag" % args.check_every),
                                   engine={L.FMT_SELL: "SELL-32-sigma", L.FMT_DICT: "row-pattern dictionary (explicit option)"}.get(last["format"], "CSR TMA-staged"),
                                   transport=(os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None)),

@@ -21,7 +21,7 @@ CGB_OK, CGB_ERR_INVALID, CGB_ERR_CUDA, CGB_ERR_NCCL, CGB_ERR_STATE, CGB_ERR_IO, 
 FMT_AUTO, FMT_CSR, FMT_SELL, FMT_DICT = 0, 1, 2, 3
 COO_MIRROR, COO_SUM_DUPLICATES, COO_COMPACT_ROWS, COO_ONE_BASED = 1, 2, 4, 8
 COO_REFERENCE_DIALECT = COO_MIRROR | COO_COMPACT_ROWS | COO_ONE_BASED
-LOOP_AUTO, LOOP_GRAPH, LOOP_PERSISTENT, LOOP_STEPWISE = 0, 1, 2, 3
+LOOP_AUTO, LOOP_GRAPH, LOOP_PERSISTENT, LOOP_STEPWISE, LOOP_CLUSTER = 0, 1, 2, 3, 4
 NCCL_ID_BYTES = 128
 
 

@@ -3,6 +3,7 @@
 // 12 device operations and one wait_and_throw per iteration; here a batch of iterations is one
 // CUDA-graph launch and the stop flag lives on the device, polled once per batch.
 #include "launch.cuh"
+#include "cluster.cuh"
 #include "persistent.cuh"
 
 #include <algorithm>
@@ -133,6 +134,64 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
   return CGB_OK;
 }
 
+// The loop inside one thread-block cluster (cluster.cuh) when the matrix and the vectors fit its shared memory.
+// *ran = false (and CGB_OK) when they do not, or the device cannot co-schedule such a cluster: the caller falls
+// back to the cooperative kernel.  CGB_CLUSTER=0 disables it, CGB_CLUSTER_CTAS picks the cluster size (A/B runs).
+template <int RPT>
+int cluster_launch(cgb_ctx *ctx, cgb_csr *A, double *d_x, int ncta, int R, int W, size_t smem, bool *ran) {
+  auto kernel = cg_cluster_kernel<RPT>;
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+      (ncta > 8 && cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)) {
+    cudaGetLastError();
+    return CGB_OK;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ncta);
+  cfg.blockDim = dim3(kClusterThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = ncta;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int clusters = 0;
+  if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) != cudaSuccess || clusters < 1) {
+    cudaGetLastError();
+    return CGB_OK;
+  }
+  Workspace &w = A->ws;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, csr_view(A), d_x, (const double *)w.r, w.st, w.hist, R, W);
+  if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "cg_cluster_kernel: %s", cudaGetErrorString(e));
+  *ran = true;
+  return CGB_OK;
+}
+
+int cluster_try_solve(cgb_ctx *ctx, cgb_csr *A, double *d_x, bool *ran) {
+  *ran = false;
+  if (const char *e = getenv("CGB_CLUSTER"))
+    if (atoi(e) == 0) return CGB_OK;
+  if (A->n_cols != A->n) return CGB_OK;
+  const int W = A->max_row;
+  if (W < 1 || W > 64) return CGB_OK;
+  int sizes[3] = {kClusterMaxCtas, 8, 0};
+  if (const char *e = getenv("CGB_CLUSTER_CTAS")) sizes[0] = std::max(1, std::min(kClusterMaxCtas, atoi(e))), sizes[1] = 0;
+  for (int i = 0; sizes[i] > 0 && !*ran; i++) {
+    const int ncta = sizes[i];
+    int R = (int)((A->n + ncta - 1) / ncta);
+    R = (R + 31) & ~31;
+    const int rpt = (R + kClusterThreads - 1) / kClusterThreads;
+    const size_t smem = cluster_smem_bytes(R, W);
+    if (R > 65536 || rpt > 4 || smem > kClusterSmemMax) continue;
+    if (rpt == 1) CGB_TRY(cluster_launch<1>(ctx, A, d_x, ncta, R, W, smem, ran));
+    else if (rpt == 2) CGB_TRY(cluster_launch<2>(ctx, A, d_x, ncta, R, W, smem, ran));
+    else CGB_TRY(cluster_launch<4>(ctx, A, d_x, ncta, R, W, smem, ran));
+  }
+  return CGB_OK;
+}
+
 } // namespace cgb
 
 extern "C" {
@@ -174,8 +233,15 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (const char *e = getenv("CGB_PERSISTENT_MAX_N")) persistent_max_n = atoll(e);
   const bool jacobi = o.jacobi != 0;
   const bool can_persist = !replace && !jacobi && ctx->coop_ok && (csr_engine(A) == kEngTma || csr_engine(A) == kEngVec) && !o.time_kernels;
-  const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
-  if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT) mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
+  // The same loop inside one thread-block cluster (cluster.cuh) when the system fits its shared memory.
+  const bool want_cluster = mode == CGB_LOOP_CLUSTER || (mode == CGB_LOOP_AUTO && n <= persistent_max_n);
+  if (mode == CGB_LOOP_CLUSTER && !can_persist)
+    return fail(CGB_ERR_UNSUPPORTED, "CGB_LOOP_CLUSTER serves plain CG on the CSR engines only");
+  const bool persistent = can_persist && (mode == CGB_LOOP_PERSISTENT || mode == CGB_LOOP_CLUSTER ||
+                                          (mode == CGB_LOOP_AUTO && n <= persistent_max_n));
+  const bool cluster_only = mode == CGB_LOOP_CLUSTER;
+  if (mode == CGB_LOOP_AUTO || mode == CGB_LOOP_PERSISTENT || mode == CGB_LOOP_CLUSTER)
+    mode = persistent ? CGB_LOOP_PERSISTENT : CGB_LOOP_GRAPH;
   const bool fused = (o.fuse_p_update != 0 && csr_panels(A) == 0 && !jacobi) || persistent; // the persistent kernel forms p in the gather (ping-pong buffers)
   CGB_TRY(workspace_ensure(A, n, fused, hist_cap));
   Workspace &w = A->ws;
@@ -268,7 +334,15 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   const int per_replace = 2 + (int)extra + (jacobi ? 1 : 0);
   double t_p = 0, t_s = 0, t_u = 0;
   int64_t samples = 0;
-  if (persistent) {
+  bool in_cluster = false;
+  if (persistent && want_cluster) CGB_TRY(cluster_try_solve(ctx, A, d_x, &in_cluster));
+  if (cluster_only && !in_cluster)
+    return fail(CGB_ERR_UNSUPPORTED, "CGB_LOOP_CLUSTER: matrix and vectors do not fit one cluster's shared memory");
+  if (in_cluster) {
+    launches += 1;
+    mode = CGB_LOOP_CLUSTER;
+  }
+  if (persistent && !in_cluster) {
     int rc = CGB_OK;
     dispatch_lanes(A->lanes, kEngVec, [&](auto Lc, auto) {
       constexpr int L = decltype(Lc)::value;

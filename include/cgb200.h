@@ -168,11 +168,14 @@ int cgb_scalar_get(cgb_ctx *ctx, const double *d_scalar, double *h_value);
  * replaces: CG::solve (src/CG.hpp:255-454) with identical stop rule: ABSOLUTE tolerance on the
  * recurrence residual, checked against r.r from the START of the iteration (one-iteration lag,
  * :396-404), NaN stops (:401), at most max_iter loop trips (reference: N+1, :436). */
-enum { CGB_LOOP_AUTO = 0, CGB_LOOP_GRAPH = 1, CGB_LOOP_PERSISTENT = 2, CGB_LOOP_STEPWISE = 3 };
+enum { CGB_LOOP_AUTO = 0, CGB_LOOP_GRAPH = 1, CGB_LOOP_PERSISTENT = 2, CGB_LOOP_STEPWISE = 3, CGB_LOOP_CLUSTER = 4 };
 
 typedef struct cgb_cg_opts {
-  int loop_mode;        /* CGB_LOOP_*: CUDA-graph batches, one persistent cooperative kernel, or
-                           one launch per kernel with a host check every check_every iterations */
+  int loop_mode;        /* CGB_LOOP_*: CUDA-graph batches, one persistent cooperative kernel, one thread-block
+                           cluster with the matrix and the vectors resident in its shared memory (systems of
+                           about 1.5 MB: CGB_ERR_UNSUPPORTED when it does not fit), or one launch per kernel
+                           with a host check every check_every iterations.  AUTO: cluster when it fits, else
+                           the cooperative kernel up to 131,072 rows, else graph batches */
   int check_every;      /* iterations per graph launch / between host polls (0 = default 32) */
   int fuse_p_update;    /* 1: p = r + beta p is formed inside the SpMV gather (2 kernels per
                            iteration, double-buffered p); 0: separate p-update kernel (3 kernels) */

@@ -22,6 +22,7 @@ X_RTOL = 1e-10
 VARIANTS = {
     "auto": dict(),                                   # small systems: the persistent cooperative kernel
     "persistent": dict(loop_mode=L.LOOP_PERSISTENT),
+    "cluster": dict(loop_mode=L.LOOP_CLUSTER),        # one thread-block cluster, everything in its shared memory
     "graph": dict(loop_mode=L.LOOP_GRAPH),
     "graph_fused": dict(loop_mode=L.LOOP_GRAPH, fuse_p_update=1),
     "stepwise": dict(loop_mode=L.LOOP_STEPWISE, check_every=5),
@@ -51,7 +52,14 @@ def test_golden_solves(ctx, path, variant):
     if "tester" in path:
         pytest.skip("tol 1e-24 trip counts are rounding-order sensitive (SURVEY.md §3.2); covered below")
     x0 = g["x0"] if g["x0"].size else None
-    cg, st = run(ctx, g["vals"], g["cols"], g["rows"], g["b"], float(g["tol"]), x0, **VARIANTS[variant])
+    try:
+        cg, st = run(ctx, g["vals"], g["cols"], g["rows"], g["b"], float(g["tol"]), x0, **VARIANTS[variant])
+    except RuntimeError as e:
+        if variant == "cluster" and "do not fit" in str(e):
+            pytest.skip("system does not fit one cluster's shared memory")
+        raise
+    if variant == "cluster":
+        assert st["loop_mode"] == L.LOOP_CLUSTER and st["kernel_launches"] == 2
     assert iters_close(st["iterations"], int(g["iterations"]))
     assert st["converged"] == 1 and st["nan_stop"] == 0
     assert rel_err(cg.extract(), g["x"]) <= X_RTOL
@@ -77,7 +85,7 @@ CASES = {
 
 
 MODES = {"graph": dict(loop_mode=L.LOOP_GRAPH), "graph_fused": dict(loop_mode=L.LOOP_GRAPH, fuse_p_update=1),
-         "persistent": dict(loop_mode=L.LOOP_PERSISTENT)}
+         "persistent": dict(loop_mode=L.LOOP_PERSISTENT), "cluster": dict(loop_mode=L.LOOP_CLUSTER)}
 
 
 @pytest.mark.parametrize("mode", sorted(MODES))
@@ -89,7 +97,13 @@ def test_solve_vs_oracle(ctx, port, name, mode):
     b = G.default_rhs(n)
     tol = rel * np.linalg.norm(b)
     o = port.cg_solve(v, c, r, b, tol, history=True)
+    if mode == "cluster" and name != "C1_p2d_128":        # 12 nnz + 24 n bytes must fit 16 x 220 KB
+        with pytest.raises(RuntimeError, match="CGB_LOOP_CLUSTER"):
+            run(ctx, v, c, r, b, tol, **MODES[mode])
+        return
     cg, st = run(ctx, v, c, r, b, tol, record_history=1, **MODES[mode])
+    if mode == "cluster":
+        assert st["loop_mode"] == L.LOOP_CLUSTER and st["kernel_launches"] == 2
     if mode == "persistent" and not name.startswith("rspd"):   # (irregular rows go to the SELL engine, graph loop)
         assert st["loop_mode"] == L.LOOP_PERSISTENT and st["kernel_launches"] == 2
     if name.startswith("rspd"):
@@ -181,6 +195,31 @@ def test_host_buffer_solve(ctx, port):
     x, st = S.solve_host(ctx, v, c, r, b, tol)
     o = port.cg_solve(v, c, r, b, tol)
     assert iters_close(st["iterations"], o["iterations"]) and rel_err(x, o["x"]) <= X_RTOL
+
+
+@pytest.mark.parametrize("ctas", [16, 8, 7])
+def test_cluster_loop_shapes(ctx, port, ctas, monkeypatch):
+    """The cluster-resident loop at other cluster sizes (rows per thread 1, 2, 4), on a matrix whose size is not a
+    multiple of anything, with empty-pattern padding (rows of 3..5 entries) and a non-zero start vector; AUTO picks
+    the cluster loop when the system fits and says so."""
+    monkeypatch.setenv("CGB_CLUSTER_CTAS", str(ctas))
+    v, c, r = G.poisson2d_5pt(125)                        # n = 15625
+    n = r.size - 1
+    rng = np.random.default_rng(9)
+    b, x0 = G.default_rhs(n), rng.standard_normal(n)
+    tol = 1e-9 * np.linalg.norm(b)
+    o = port.cg_solve(v, c, r, b, tol, x0=x0, history=True)
+    cg, st = run(ctx, v, c, r, b, tol, x0, record_history=1)            # AUTO
+    assert st["loop_mode"] == L.LOOP_CLUSTER and st["kernel_launches"] == 2
+    assert iters_close(st["iterations"], o["iterations"]) and st["converged"] == 1
+    assert rel_err(cg.extract(), o["x"]) <= X_RTOL
+    h = cg.history()
+    k = min(h.size, o["hist"].size, 25)
+    assert np.allclose(h[:k], o["hist"][:k], rtol=1e-8, atol=0)
+    # bit-reproducible from run to run
+    cg.setInital(x0)
+    st2 = cg.solve(tol)
+    assert st2["iterations"] == st["iterations"] and st2["rr"] == st["rr"]
 
 
 def test_full_size_properties_C2(ctx):

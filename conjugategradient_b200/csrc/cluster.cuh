@@ -18,8 +18,8 @@
 //   -- cluster barrier, the same exchange: rr', the reference's stop rule on the OLD rr (:396-404), beta = rr'/rr (:414)
 //
 // Two barriers per trip, no global-memory traffic inside the loop.  Measured at C1: 3.5 us per trip against 6.8 us for
-// the cooperative kernel; what is left is the dependent fp64 chain of the two reductions (5 + 5 + 4 tree levels and a
-// division each, ~1.6 us per reduction whatever the number of rows: 4,096 rows take 3.3 us per trip).  Reductions are fixed-order (warp tree, warps in
+// the cooperative kernel; what is left is the two reductions (two block-level trees, the exchange, the barrier, a
+// butterfly and a division: ~1.6 us each whatever the number of rows — 4,096 rows take 3.3 us per trip).  Reductions are fixed-order (warp tree, warps in
 // order, CTAs in rank order): bit-reproducible, every thread ends up with identical scalars.  Row sums are the
 // same left-to-right FMA chain as the one-lane CSR engines.
 #pragma once
@@ -41,9 +41,9 @@ __host__ __device__ constexpr size_t cluster_smem_bytes(int R, int W) {
 
 // Publishes this CTA's sum of v in slot [rank] of every CTA's `part` array and waits for everybody's (cluster
 // barrier).  After it, part[0 .. ncta) holds the same numbers in every CTA; the caller sums them in rank order in
-// ONE thread and hands the derived scalars to the CTA through shared memory.  (fp64 issue is what bounds this loop —
-// one SM serves 1,024 rows and B200 issues a warp-wide fp64 instruction only every ~16 cycles per scheduler — so the
-// divisions and the square root of the stop rule must not be repeated by 1,024 threads.)
+// ONE thread and hands the derived scalars to the CTA through shared memory.  (One SM serves 1,024 rows here: 32 warps
+// share four schedulers, and two fp64 divisions plus the square root of the stop rule repeated by every thread
+// issued more instructions than the SpMV.)
 __device__ __forceinline__ void cluster_publish(cg::cluster_group &cl, double v, double *red, double *part, int rank, int ncta) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   v = warp_sum(v);

@@ -137,9 +137,9 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
 // The loop inside one thread-block cluster (cluster.cuh) when the matrix and the vectors fit its shared memory.
 // *ran = false (and CGB_OK) when they do not, or the device cannot co-schedule such a cluster: the caller falls
 // back to the cooperative kernel.  CGB_CLUSTER=0 disables it, CGB_CLUSTER_CTAS picks the cluster size (A/B runs).
-template <int RPT>
+template <int RPT, int TPB>
 int cluster_launch(cgb_ctx *ctx, cgb_csr *A, double *d_x, int ncta, int R, int W, size_t smem, bool *ran) {
-  auto kernel = cg_cluster_kernel<RPT>;
+  auto kernel = cg_cluster_kernel<RPT, TPB>;
   if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
       (ncta > 8 && cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)) {
     cudaGetLastError();
@@ -147,7 +147,7 @@ int cluster_launch(cgb_ctx *ctx, cgb_csr *A, double *d_x, int ncta, int R, int W
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(ncta);
-  cfg.blockDim = dim3(kClusterThreads);
+  cfg.blockDim = dim3(TPB);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = ctx->stream;
   cudaLaunchAttribute attr[1];
@@ -182,12 +182,20 @@ int cluster_try_solve(cgb_ctx *ctx, cgb_csr *A, double *d_x, bool *ran) {
     const int ncta = sizes[i];
     int R = (int)((A->n + ncta - 1) / ncta);
     R = (R + 31) & ~31;
-    const int rpt = (R + kClusterThreads - 1) / kClusterThreads;
     const size_t smem = cluster_smem_bytes(R, W);
-    if (R > 65536 || rpt > 4 || smem > kClusterSmemMax) continue;
-    if (rpt == 1) CGB_TRY(cluster_launch<1>(ctx, A, d_x, ncta, R, W, smem, ran));
-    else if (rpt == 2) CGB_TRY(cluster_launch<2>(ctx, A, d_x, ncta, R, W, smem, ran));
-    else CGB_TRY(cluster_launch<4>(ctx, A, d_x, ncta, R, W, smem, ran));
+    if (R > 65536 || smem > kClusterSmemMax) continue;
+    // threads per CTA: a row per thread where 1,024 threads allow it, and no more warps than that needs (C1, 1,024
+    // rows per CTA: 3.5 us per trip with 1,024 or 512 threads, 4.5 with 256; 256 rows per CTA: 2.9 us with 256
+    // threads, 3.3 with 1,024); CGB_CLUSTER_THREADS overrides (A/B runs)
+    int threads = R <= 256 ? 256 : R <= 512 ? 512 : 1024;
+    if (const char *e = getenv("CGB_CLUSTER_THREADS")) threads = atoi(e) >= 1024 ? 1024 : atoi(e) >= 512 ? 512 : 256;
+    const int rpt = (R + threads - 1) / threads;
+    if (rpt > 4) continue;
+#define CGB_CL_LAUNCH(T)                                                                                                 \
+  (rpt == 1 ? cluster_launch<1, T>(ctx, A, d_x, ncta, R, W, smem, ran)                                                   \
+            : rpt == 2 ? cluster_launch<2, T>(ctx, A, d_x, ncta, R, W, smem, ran) : cluster_launch<4, T>(ctx, A, d_x, ncta, R, W, smem, ran))
+    CGB_TRY(threads == 256 ? CGB_CL_LAUNCH(256) : threads == 512 ? CGB_CL_LAUNCH(512) : CGB_CL_LAUNCH(1024));
+#undef CGB_CL_LAUNCH
   }
   return CGB_OK;
 }

@@ -67,8 +67,8 @@ __device__ __forceinline__ double cluster_total(const double *part, int ncta) {
   return t;
 }
 
-template <int RPT>
-__global__ void __launch_bounds__(kClusterThreads, 1)
+template <int RPT, int TPB>
+__global__ void __launch_bounds__(TPB, 1)
     cg_cluster_kernel(CsrView A, double *__restrict__ x, const double *__restrict__ r_g, CgState *st, double *hist, int R, int W) {
   cg::cluster_group cl = cg::this_cluster();
   extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(kClusterThreads, 1)
   double xi[RPT], ri[RPT], pi[RPT], api[RPT];
 #pragma unroll
   for (int k = 0; k < RPT; k++) {
-    const int lt = t + k * kClusterThreads;
+    const int lt = t + k * TPB;
     const int64_t row = base + lt;
     const bool live = lt < R && row < A.n;
     xi[k] = live ? x[row] : 0.0;
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(kClusterThreads, 1)
     double a = 0.0;
 #pragma unroll
     for (int k = 0; k < RPT; k++) {
-      const int lt = t + k * kClusterThreads;
+      const int lt = t + k * TPB;
       if (lt < R) {
         pi[k] = fma(beta, pi[k], ri[k]);
         p_new_s[lt] = pi[k];
@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(kClusterThreads, 1)
     double acc = 0.0;
 #pragma unroll
     for (int k = 0; k < RPT; k++) {
-      const int lt = t + k * kClusterThreads;
+      const int lt = t + k * TPB;
       if (lt < R) {
         xi[k] = fma(alpha, pi[k], xi[k]);
         ri[k] = fma(-alpha, api[k], ri[k]);
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kClusterThreads, 1)
   }
 #pragma unroll
   for (int k = 0; k < RPT; k++) {
-    const int lt = t + k * kClusterThreads;
+    const int lt = t + k * TPB;
     const int64_t row = base + lt;
     if (lt < R && row < A.n) x[row] = xi[k];
   }

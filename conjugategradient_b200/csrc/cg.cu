@@ -164,7 +164,10 @@ int cluster_launch(cgb_ctx *ctx, cgb_csr *A, double *d_x, int ncta, int R, int W
   }
   Workspace &w = A->ws;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, csr_view(A), d_x, (const double *)w.r, w.st, w.hist, R, W);
-  if (e != cudaSuccess) return fail(CGB_ERR_CUDA, "cg_cluster_kernel: %s", cudaGetErrorString(e));
+  if (e != cudaSuccess) { // a launch-time refusal (e.g. no 16 free SMs in one GPC under MPS): the caller falls back
+    cudaGetLastError();
+    return CGB_OK;
+  }
   *ran = true;
   return CGB_OK;
 }
@@ -345,7 +348,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   bool in_cluster = false;
   if (persistent && want_cluster) CGB_TRY(cluster_try_solve(ctx, A, d_x, &in_cluster));
   if (cluster_only && !in_cluster)
-    return fail(CGB_ERR_UNSUPPORTED, "CGB_LOOP_CLUSTER: matrix and vectors do not fit one cluster's shared memory");
+    return fail(CGB_ERR_UNSUPPORTED, "CGB_LOOP_CLUSTER: matrix and vectors do not fit one cluster's shared memory (or the device refused the cluster launch)");
   if (in_cluster) {
     launches += 1;
     mode = CGB_LOOP_CLUSTER;

@@ -187,10 +187,10 @@ int cluster_try_solve(cgb_ctx *ctx, cgb_csr *A, double *d_x, bool *ran) {
     R = (R + 31) & ~31;
     const size_t smem = cluster_smem_bytes(R, W);
     if (R > 65536 || smem > kClusterSmemMax) continue;
-    // threads per CTA: a row per thread where 1,024 threads allow it, and no more warps than that needs (C1, 1,024
-    // rows per CTA: 3.5 us per trip with 1,024 or 512 threads, 4.5 with 256; 256 rows per CTA: 2.9 us with 256
-    // threads, 3.3 with 1,024); CGB_CLUSTER_THREADS overrides (A/B runs)
-    int threads = R <= 256 ? 256 : R <= 512 ? 512 : 1024;
+    // threads per CTA (C1, 1,024 rows per CTA: 3.4 us per trip with 512 threads, 3.6 with 1,024, 4.1 with 256 — fewer
+    // warps make the block reductions and the barriers cheaper, up to the point where a thread's rows serialise;
+    // 256 rows per CTA: 2.9 us with 256 threads, 3.3 with 1,024); CGB_CLUSTER_THREADS overrides (A/B runs)
+    int threads = R <= 256 ? 256 : R <= 1024 ? 512 : 1024;
     if (const char *e = getenv("CGB_CLUSTER_THREADS")) threads = atoi(e) >= 1024 ? 1024 : atoi(e) >= 512 ? 512 : 256;
     const int rpt = (R + threads - 1) / threads;
     if (rpt > 4) continue;

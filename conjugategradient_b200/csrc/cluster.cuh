@@ -102,8 +102,8 @@ __global__ void __launch_bounds__(TPB, 1)
           const int c = A.cols[b + j];
           cols_s[idx] = (c / R) << 16 | (c % R); // owner CTA | index in the owner's slice
           vals_s[idx] = A.vals[b + j];
-        } else {
-          cols_s[idx] = -1;
+        } else { // no entry: a harmless address (this row's own slot) with the sign bit set
+          cols_s[idx] = (int)(0x80000000u | (unsigned)rank << 16 | (unsigned)lt);
           vals_s[idx] = 0.0;
         }
       }
@@ -130,20 +130,25 @@ __global__ void __launch_bounds__(TPB, 1)
       if (lt < R) {
         pi[k] = fma(beta, pi[k], ri[k]);
         p_new_s[lt] = pi[k];
-        double sum = 0.0;
-        for (int j = 0; j < W; j++) {
+      }
+      api[k] = 0.0;
+    }
+    for (int j = 0; j < W; j++) { // the rows of a thread advance together: their gathers overlap
+#pragma unroll
+      for (int k = 0; k < RPT; k++) {
+        const int lt = t + k * TPB;
+        if (lt < R) {
           const int c = cols_s[(size_t)j * R + lt];
-          if (c >= 0) {
-            const double *owner = cl.map_shared_rank(vec_s, c >> 16);
-            const int l = c & 0xffff;
-            const double pj = fma(beta, owner[off_old + l], owner[l]); // p = r + beta p_old, as the owner rounds it
-            sum = fma(vals_s[(size_t)j * R + lt], pj, sum);
-          }
+          const double *owner = cl.map_shared_rank(vec_s, (c >> 16) & 0x7fff);
+          const int l = c & 0xffff;
+          const double pj = fma(beta, owner[off_old + l], owner[l]); // p = r + beta p_old, as the owner rounds it
+          const double s1 = fma(vals_s[(size_t)j * R + lt], pj, api[k]);
+          api[k] = c < 0 ? api[k] : s1;
         }
-        api[k] = sum;
-        a = fma(pi[k], sum, a);
       }
     }
+#pragma unroll
+    for (int k = 0; k < RPT; k++) a = fma(pi[k], api[k], a);
     cluster_publish(cl, a, red, part_b, rank, ncta);
     if (t < 32) {
       const double pAp = cluster_total(part_b, ncta);

@@ -13,15 +13,15 @@
 //   phase B   p_i = r_i + beta p_i; p_new_s[i] = p_i; Ap_i = sum_j a_ij (r_s[c] + beta p_old_s[c]) with the gathers going
 //             to the owner CTA's shared memory (p formed in the gather like persistent.cuh, so no barrier is
 //             needed between the p-update and the product); partial of p.Ap            (src/CG.hpp:374-379, :418)
-//   -- cluster barrier: every CTA has written its partial into every CTA's slot array; all sum them in rank order
+//   -- cluster barrier: every CTA has written its partial into every CTA's slot array; warp 0 of each sums them
 //   phase C   alpha = rr / p.Ap; x_i += alpha p_i; r_i -= alpha Ap_i; r_s[i] = r_i; partial of r.r  (:385-392, :406)
 //   -- cluster barrier, the same exchange: rr', the reference's stop rule on the OLD rr (:396-404), beta = rr'/rr (:414)
 //
-// Two barriers per trip, no global-memory traffic inside the loop.  Measured at C1: 3.5 us per trip against 6.8 us for
+// Two barriers per trip, no global-memory traffic inside the loop.  Measured at C1: 3.4 us per trip against 6.8 us for
 // the cooperative kernel; what is left is the two reductions (two block-level trees, the exchange, the barrier, a
-// butterfly and a division: ~1.6 us each whatever the number of rows — 4,096 rows take 3.3 us per trip).  Reductions are fixed-order (warp tree, warps in
-// order, CTAs in rank order): bit-reproducible, every thread ends up with identical scalars.  Row sums are the
-// same left-to-right FMA chain as the one-lane CSR engines.
+// butterfly and a division: ~2,500 cycles each, tools/cluster_sync_bench.cu) whatever the number of rows.
+// Reductions are fixed-order (warp tree, warps in order, a butterfly over the CTAs): bit-reproducible, every CTA
+// derives identical scalars.  Row sums are the same left-to-right FMA chain as the one-lane CSR engines.
 #pragma once
 #include <cooperative_groups.h>
 
@@ -31,7 +31,6 @@ namespace cgb {
 
 namespace cg = cooperative_groups;
 
-constexpr int kClusterThreads = 1024;
 constexpr int kClusterMaxCtas = 16;
 constexpr size_t kClusterSmemMax = 220 * 1024; // per CTA, dynamic
 

@@ -438,14 +438,28 @@ def run_ours(args, kind, m, rel):
                 L.check(lib.cgb_cg_solve_host(ctx.h, nloc, nnz_loc, pv.ctypes.data, pc.ctypes.data, pr.ctypes.data,
                                               pb.ctypes.data, None, px.ctypes.data, tol, -1, C.byref(e_opts), C.byref(e_stats)))
             else:
+                trace = rank == 0 and os.environ.get("CGB_DIST_TIMING")  # debug: wall time of each call (adds syncs)
+                t_prev = [time.perf_counter()]
+
+                def mark(what):
+                    if trace:
+                        ctx.sync()
+                        now = time.perf_counter()
+                        print(f"[bench e2e timing] {what:<28s} {1e3 * (now - t_prev[0]):8.2f} ms", file=sys.stderr, flush=True)
+                        t_prev[0] = now
                 a2 = C.c_void_p()
                 L.check(lib.cgb_csr_create(ctx.h, nloc, nnz_loc, pv.ctypes.data, pc.ctypes.data, pr.ctypes.data, C.byref(a2)))
+                mark("cgb_csr_create (H2D)")
                 L.check(lib.cgb_dist_set_matrix(dh, row_starts.ctypes.data_as(C.c_void_p), a2))
+                mark("cgb_dist_set_matrix")
                 lib.cgb_csr_destroy(a2)
+                mark("cgb_csr_destroy")
                 L.check(lib.cgb_memcpy_h2d(ctx.h, bvec.ptr, pb.ctypes.data, 8 * nloc, 0))
                 L.check(lib.cgb_memset(ctx.h, xvec.ptr, 0, 8 * nloc))
                 L.check(lib.cgb_dist_cg_solve(dh, bvec.ptr, xvec.ptr, tol, -1, C.byref(e_opts), C.byref(e_stats)))
+                mark("b H2D + cgb_dist_cg_solve")
                 L.check(lib.cgb_memcpy_d2h(ctx.h, px.ctypes.data, xvec.ptr, 8 * nloc, 1))
+                mark("x D2H")
             return e_stats.as_dict()
 
         if dh is None:

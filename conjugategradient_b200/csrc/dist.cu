@@ -23,6 +23,8 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <vector>
 
 using namespace cgb;

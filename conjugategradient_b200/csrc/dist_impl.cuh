@@ -14,6 +14,21 @@ struct DevBuf { // frees on scope exit
   template <class T> T *as() { return (T *)p; }
 };
 
+// CGB_DIST_TIMING=1: rank 0 prints the wall time of the set-up phases (stream-synchronised) to stderr
+struct PhaseTimer {
+  bool on;
+  cudaStream_t s;
+  std::chrono::steady_clock::time_point t;
+  PhaseTimer(const cgb_dist *d) : on(getenv("CGB_DIST_TIMING") != nullptr && d->rank == 0), s(d->ctx->stream), t(std::chrono::steady_clock::now()) {}
+  void mark(const char *what) {
+    if (!on) return;
+    cudaStreamSynchronize(s);
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[cgb dist timing] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t).count());
+    t = now;
+  }
+};
+
 int dev_alloc(DevBuf &b, size_t bytes) {
   CGB_CUDA(cudaMalloc(&b.p, bytes ? bytes : 16));
   return CGB_OK;
@@ -148,6 +163,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   const int lo = (int)d->row_starts[d->rank], hi = (int)d->row_starts[d->rank + 1];
   const int tb = 256;
   const unsigned gb = (unsigned)std::max<int64_t>(1, (n + tb - 1) / tb);
+  PhaseTimer pt(d);
   DevBuf b_cl, b_cr, b_flag, b_slot, b_tmp, b_rem, b_rem_sorted, b_num, b_cnt_compact;
   CGB_TRY(dev_alloc(b_cl, sizeof(int) * (size_t)(n + 1)));
   CGB_TRY(dev_alloc(b_cr, sizeof(int) * (size_t)(n + 1)));
@@ -171,6 +187,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   cub::DeviceSelect::If(nullptr, t, nullp, nullp, nullp, ni, NonZero{}, s); tmp_bytes = std::max(tmp_bytes, t);
   CGB_TRY(dev_alloc(b_tmp, tmp_bytes));
 
+  pt.mark("setup: count local/remote");
   // A_loc row offsets
   DevBuf g_rl, g_rh, g_cl, g_vl, g_ch, g_vh; // own the new arrays until the two handles below take them over
   int32_t *rowptr_loc = nullptr;
@@ -204,6 +221,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
     cub::DeviceScan::InclusiveSum(b_tmp.p, t, rowptr_halo + 1, rowptr_halo + 1, nh, s);
   }
 
+  pt.mark("setup: row offsets");
   // receive list: sorted distinct remote columns
   CGB_TRY(dev_alloc(b_rem, sizeof(int) * (size_t)(nnz_halo + 1)));
   CGB_TRY(dev_alloc(b_rem_sorted, sizeof(int) * (size_t)(nnz_halo + 1)));
@@ -229,6 +247,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   }
   d->H = H;
 
+  pt.mark("setup: receive list");
   // fill both parts
   int32_t *cols_loc = nullptr, *cols_halo = nullptr;
   double *vals_loc = nullptr, *vals_halo = nullptr;
@@ -246,6 +265,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
                                         slot, rowptr_halo, cols_halo, vals_halo, d->halo_rows, recv_cols, H);
     CGB_CUDA(cudaGetLastError());
   }
+  pt.mark("setup: fill local + halo");
   CGB_TRY(cgb_csr_from_device(ctx, n, nnz_loc, vals_loc, cols_loc, rowptr_loc, 1, &d->Aloc));
   g_rl.p = g_cl.p = g_vl.p = nullptr;
   CGB_TRY(cgb_csr_from_device(ctx, nh, nnz_halo, vals_halo, cols_halo, rowptr_halo, 1, &d->Ahalo));
@@ -259,6 +279,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
     if (rc != CGB_OK && rc != CGB_ERR_UNSUPPORTED) return rc;
   }
 
+  pt.mark("setup: handles + format");
   // who sends what: receive counts per owner, all-gathered into a matrix
   std::vector<int32_t> h_recv;
   CGB_TRY(d2h_vec(ctx, h_recv, recv_cols, (size_t)H));
@@ -299,7 +320,9 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
     CGB_CUDA(cudaGetLastError());
   }
   CGB_CUDA(cudaStreamSynchronize(s));
+  pt.mark("setup: send/receive plan");
   if (d->peer) CGB_TRY(peer_halo_setup(d, M));
+  pt.mark("setup: peer halo mapping");
   return CGB_OK;
 }
 
@@ -391,7 +414,9 @@ int cgb_dist_set_matrix(cgb_dist *d, const int64_t *row_starts, cgb_csr *A) {
   CGB_REQUIRE(row_starts[d->rank + 1] - row_starts[d->rank] == A->n, "cgb_dist_set_matrix: row block size mismatch");
   CGB_REQUIRE(row_starts[d->nranks] < ((int64_t)1 << 31), "cgb_dist_set_matrix: global size must fit 32-bit columns");
   ScopedDevice sd(d->ctx->device);
+  PhaseTimer pt(d);
   dist_release_matrix(d);
+  pt.mark("set_matrix: release old");
   d->n = A->n;
   d->row_starts.assign(row_starts, row_starts + d->nranks + 1);
   return dist_setup(d, A);
@@ -415,8 +440,10 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   int batch = o.check_every > 0 ? o.check_every : 32;
   if ((int64_t)batch > max_iter) batch = (int)std::max<int64_t>(1, max_iter);
   const int64_t hist_cap = o.record_history ? max_iter + 1 : 0;
+  PhaseTimer pt(d);
   CGB_TRY(csr_prepare(A));
   if (d->Ahalo) CGB_TRY(csr_prepare(d->Ahalo));
+  pt.mark("solve: prepare engines");
   CGB_TRY(workspace_ensure(A, n, false, hist_cap));
   Workspace &w = A->ws;
   const bool use_graph = o.loop_mode != CGB_LOOP_STEPWISE;
@@ -480,6 +507,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     w.graph_key = gkey;
     w.graph_x = d_x;
   }
+  pt.mark("solve: workspace, K0, graph");
   // every rank takes the same decisions: the polled state is built from all-reduced scalars only
   while (true) {
     if (use_graph) {
@@ -500,6 +528,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   launches += 1;
   CGB_CUDA(cudaEventRecord(t1, s));
   CGB_CUDA(cudaEventSynchronize(t1));
+  pt.mark("solve: iterations");
   const CgState &f = w.h_st[0];
   w.hist_count = o.record_history ? std::min<int64_t>(f.iter + 1, w.hist_cap) : 0;
   if (stats) {

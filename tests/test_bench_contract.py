@@ -1,0 +1,48 @@
+"""bench.py prints exactly ONE JSON line on stdout carrying the keys the driver reads (both arms)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BASE_KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+             "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"}
+
+
+def run_bench(*args, timeout=600):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], capture_output=True, text=True,
+                         timeout=timeout, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-3000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, out.stdout[-2000:]
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line():
+    """The reference arm: the reference's own CPU solver (oracle/_ref, else the C restatement) on the host cores."""
+    d = run_bench("--impl", "reference", "--workload", "poisson2d_5pt_128", "--steps", "1", "--warmup", "1")
+    assert BASE_KEYS <= set(d) and d["impl"] == "reference"
+    assert d["metric"] == "cg_iterations_per_sec" and d["unit"] == "iterations/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["steps"] == 1 and d["warmup"] == 1 and d["dtype"] == "f64"
+    assert d["config"]["workload"] == "poisson2d_5pt_128" and d["config"]["n"] == 16384
+    cb = d["cpu_baseline"]
+    assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["sample"] and cb["value"] == d["value"]
+    e = d["e2e"]
+    assert e["value"] == d["value"] and e["unit"] == d["unit"] and e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
+
+
+@pytest.mark.gpu
+def test_our_arm_line():
+    """Our arm on the small configuration: roofline, cpu_baseline, e2e, launch count and clocks are all there."""
+    d = run_bench("--workload", "poisson2d_5pt_128", "--steps", "3", "--warmup", "3", "--cpu-seconds", "2")
+    assert BASE_KEYS | {"roofline", "gpu_launches", "clocks"} <= set(d) and d.get("impl", "ours") == "ours"
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["gpu_launches"] > 0
+    r = d["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and r["peak"] > 0 and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    cb = d["cpu_baseline"]
+    assert cb["value"] > 0 and cb["cores"] >= 1 and cb["kind"] in ("reference", "port") and cb["sample"]
+    e = d["e2e"]
+    assert e["value"] > 0 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] == 8 * d["config"]["n"]
+    assert d["config"]["iterations_per_solve"] == 366 and d["config"]["true_rel_residual"] <= 2e-8

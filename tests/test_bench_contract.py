@@ -29,6 +29,7 @@ def test_reference_arm_line():
     assert d["config"]["workload"] == "poisson2d_5pt_128" and d["config"]["n"] == 16384
     cb = d["cpu_baseline"]
     assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["sample"] and cb["value"] == d["value"]
+    assert d["run"]["trips_per_step"] >= 32          # the reference's per-solve set-up must not dominate the sample
     e = d["e2e"]
     assert e["value"] == d["value"] and e["unit"] == d["unit"] and e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
 
@@ -36,7 +37,7 @@ def test_reference_arm_line():
 @pytest.mark.gpu
 def test_our_arm_line():
     """Our arm on the small configuration: roofline, cpu_baseline, e2e, launch count and clocks are all there."""
-    d = run_bench("--workload", "poisson2d_5pt_128", "--steps", "3", "--warmup", "3", "--cpu-seconds", "2")
+    d = run_bench("--workload", "poisson2d_5pt_128", "--steps", "3", "--warmup", "3", "--cpu-seconds", "2", "--configs", "none")
     assert BASE_KEYS | {"roofline", "gpu_launches", "clocks"} <= set(d) and d.get("impl", "ours") == "ours"
     assert d["value"] > 0 and d["n_gpus"] == 1 and d["gpu_launches"] > 0
     r = d["roofline"]
@@ -45,4 +46,23 @@ def test_our_arm_line():
     assert cb["value"] > 0 and cb["cores"] >= 1 and cb["kind"] in ("reference", "port") and cb["sample"]
     e = d["e2e"]
     assert e["value"] > 0 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] == 8 * d["config"]["n"]
-    assert d["config"]["iterations_per_solve"] == 366 and d["config"]["true_rel_residual"] <= 2e-8
+    assert d["run"]["iterations_per_solve"] == 366 and d["run"]["true_rel_residual"] <= 2e-8
+    assert 0 < r["frac"] <= 1.2
+    # parity block: checksums of x after the full solve and after the first k trips, held against the reference
+    p = d["parity"]
+    assert p["ok"] is True and p["first_k"]["k"] == 32 and p["vs_reference_live"]["x_rel_err"] <= 1e-10
+    assert p["vs_reference_fixture"]["x_norm2_rel_diff"] <= 1e-10
+    assert d["configs"] == {}            # --configs none below
+
+
+def test_both_arms_describe_the_same_config():
+    """`config` is the workload in the same words in both arms (the driver compares them)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    c = b.config_dict("poisson3d_7pt_512", "3d7", 512, 512 ** 3, 937951232, 1e-8, 1)
+    assert c["B_iter_bytes"] == 23603445764 and c["baseline_config"] == "C4"
+    assert not ({"where", "iterations_per_solve", "true_rel_residual", "loop", "engine", "transport"} & set(c))   # per-run facts live in `run`
+    w = b.counter_w(5, 1000)
+    assert w.min() >= -1.0 and w.max() < 1.0 and abs(w.mean()) < 0.1 and (b.counter_w(0, 1000)[5:] == w).all()

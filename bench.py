@@ -604,6 +604,7 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
     bvec.free()
     xvec.free()
     A.free()
+    lib.cgb_trim()  # the library caches freed device blocks for re-use: hand them back before the next workload
     run = {"where": f"{world}xB200", "iterations_per_solve": last["iterations"], "true_rel_residual": true_rel,
            "loop": ("one thread-block cluster per solve (cluster barriers, distributed shared memory)" if last["loop_mode"] == L.LOOP_CLUSTER
                     else "one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT

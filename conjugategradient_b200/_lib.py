@@ -59,6 +59,7 @@ SIGNATURES = {
     "cgb_ctx_sm_count": (C.c_int, [c_vp]),
     "cgb_malloc": (C.c_int, [c_vp, C.c_size_t, C.POINTER(c_vp)]),
     "cgb_free": (C.c_int, [c_vp, c_vp]),
+    "cgb_trim": (C.c_int, []),
     "cgb_memcpy_h2d": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t, C.c_int]),
     "cgb_memcpy_d2h": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t, C.c_int]),
     "cgb_memcpy_d2d": (C.c_int, [c_vp, c_vp, c_vp, C.c_size_t]),

@@ -101,6 +101,21 @@ struct ScopedDevice {
 
 int ctx_scratch(cgb_ctx *ctx); // allocates ctx->partials / ticket on first use
 
+// ---- device-memory cache (core.cu) -------------------------------------------------------------------------
+// Every cudaMalloc / cudaFree of the library goes through a per-device cache of whole allocations keyed by size:
+// a freed block is kept and handed out again for a request of (nearly) the same size.  The end-to-end paths
+// (cgb_cg_solve_host, cgb_dist_set_matrix: a matrix, its work vectors and their scratch per call) then cost no
+// driver allocation after the first call — cudaFree of a multi-GB block alone is milliseconds.  Semantics are
+// cudaFree's: the device is synchronised before a block changes hands.  Blocks are never split, so a cached
+// block is still a legal argument of cudaIpcGetMemHandle.  CGB_ALLOC_CACHE=0 disables it, CGB_ALLOC_CACHE_MAX_GB
+// bounds what is kept (default 64), cgb_trim() returns everything to the driver; an allocation the driver refuses
+// is retried once after a trim.
+cudaError_t cached_malloc(void **p, size_t bytes);
+cudaError_t cached_free(void *p);
+cudaError_t cached_host_alloc(void **p, size_t bytes);
+cudaError_t cached_host_free(void *p);
+void cache_trim();
+
 #ifdef __CUDACC__
 // ---- device helpers ------------------------------------------------------------------------
 // Streaming (read-once) loads: bypass L1 allocation so the gathered vector keeps the cache.
@@ -173,3 +188,8 @@ __device__ __forceinline__ bool publish_and_elect(unsigned int *ticket, int nblo
 #endif // __CUDACC__
 
 } // namespace cgb
+
+#ifndef CGB_NO_ALLOC_MACROS
+#define cudaMalloc(p, bytes) ::cgb::cached_malloc((void **)(p), (bytes))
+#define cudaFree(p) ::cgb::cached_free((void *)(p))
+#endif

@@ -1,9 +1,14 @@
 // core.cu — context, device memory, events, error reporting of the cgb200 C-ABI.
 // Interfaces replaced: acpp::sycl::queue / malloc_device / free / copy / fill / event as used by
 // the reference in src/LinearAlgebraTypes.hpp:43-49,101-121,160-183,213-224 and src/CG.hpp:561-578.
+#define CGB_NO_ALLOC_MACROS
 #include "common.cuh"
 
 #include <stdarg.h>
+
+#include <map>
+#include <mutex>
+#include <unordered_map>
 
 namespace cgb {
 
@@ -27,10 +32,149 @@ int fail(int code, const char *fmt, ...) {
 int ctx_scratch(cgb_ctx *ctx) {
   if (ctx->partials) return CGB_OK;
   ScopedDevice sd(ctx->device);
-  CGB_CUDA(cudaMalloc(&ctx->partials, sizeof(double) * 2 * kMaxPartials));
-  CGB_CUDA(cudaMalloc(&ctx->ticket, sizeof(unsigned int) * 4));
+  CGB_CUDA(cached_malloc((void **)&ctx->partials, sizeof(double) * 2 * kMaxPartials));
+  CGB_CUDA(cached_malloc((void **)&ctx->ticket, sizeof(unsigned int) * 4));
   CGB_CUDA(cudaMemsetAsync(ctx->ticket, 0, sizeof(unsigned int) * 4, ctx->stream));
   return CGB_OK;
+}
+
+// ---- device-memory cache (see common.cuh) ---------------------------------------------------------------------
+namespace {
+struct DevCache {
+  std::multimap<size_t, void *> free_blocks;   // size -> block
+  std::unordered_map<void *, size_t> live;     // blocks handed out
+  size_t cached_bytes = 0;
+};
+struct AllocCache {
+  std::mutex mu;
+  std::map<int, DevCache> dev;
+  std::multimap<size_t, void *> host_free;
+  std::unordered_map<void *, size_t> host_live;
+  bool on = true;
+  size_t max_bytes = (size_t)64 << 30;
+  AllocCache() {
+    if (const char *e = getenv("CGB_ALLOC_CACHE")) on = atoi(e) != 0;
+    if (const char *e = getenv("CGB_ALLOC_CACHE_MAX_GB")) max_bytes = (size_t)(atof(e) * (double)((size_t)1 << 30));
+  }
+};
+AllocCache &alloc_cache() {
+  static AllocCache *c = new AllocCache(); // never destroyed: frees may come from static destructors
+  return *c;
+}
+void trim_device_locked(DevCache &d, size_t keep) {
+  while (d.cached_bytes > keep && !d.free_blocks.empty()) {
+    auto it = std::prev(d.free_blocks.end()); // largest first
+    cudaFree(it->second);
+    d.cached_bytes -= it->first;
+    d.free_blocks.erase(it);
+  }
+}
+} // namespace
+
+cudaError_t cached_malloc(void **p, size_t bytes) {
+  AllocCache &c = alloc_cache();
+  if (!c.on) return cudaMalloc(p, bytes);
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const size_t want = ((bytes ? bytes : 1) + 511) & ~(size_t)511;
+  std::lock_guard<std::mutex> lk(c.mu);
+  DevCache &d = c.dev[dev];
+  auto it = d.free_blocks.lower_bound(want);
+  if (it != d.free_blocks.end() && it->first <= want + want / 4 + 4096) {
+    *p = it->second;
+    d.cached_bytes -= it->first;
+    d.live[it->second] = it->first;
+    d.free_blocks.erase(it);
+    return cudaSuccess;
+  }
+  e = cudaMalloc(p, want);
+  if (e != cudaSuccess) { // out of memory with blocks parked in the cache: give them back and try once more
+    cudaGetLastError();
+    cudaDeviceSynchronize();
+    trim_device_locked(d, 0);
+    e = cudaMalloc(p, want);
+  }
+  if (e == cudaSuccess) d.live[*p] = want;
+  return e;
+}
+
+cudaError_t cached_free(void *p) {
+  if (!p) return cudaSuccess;
+  AllocCache &c = alloc_cache();
+  if (!c.on) return cudaFree(p);
+  cudaPointerAttributes at;
+  int dev = 0;
+  if (cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeDevice) dev = at.device;
+  else {
+    cudaGetLastError();
+    cudaGetDevice(&dev);
+  }
+  std::unique_lock<std::mutex> lk(c.mu);
+  DevCache &d = c.dev[dev];
+  auto it = d.live.find(p);
+  if (it == d.live.end()) { // not ours (e.g. adopted from the caller): the driver's own free
+    lk.unlock();
+    return cudaFree(p);
+  }
+  const size_t sz = it->second;
+  d.live.erase(it);
+  lk.unlock();
+  cudaError_t e = cudaDeviceSynchronize(); // cudaFree's semantics: nothing in flight touches the block once it changes hands
+  lk.lock();
+  d.free_blocks.emplace(sz, p);
+  d.cached_bytes += sz;
+  if (d.cached_bytes > c.max_bytes) trim_device_locked(d, c.max_bytes);
+  return e;
+}
+
+cudaError_t cached_host_alloc(void **p, size_t bytes) {
+  AllocCache &c = alloc_cache();
+  const size_t want = ((bytes ? bytes : 1) + 4095) & ~(size_t)4095;
+  if (c.on && want <= ((size_t)1 << 20)) {
+    std::lock_guard<std::mutex> lk(c.mu);
+    auto it = c.host_free.find(want);
+    if (it != c.host_free.end()) {
+      *p = it->second;
+      c.host_live[*p] = want;
+      c.host_free.erase(it);
+      return cudaSuccess;
+    }
+    cudaError_t e = cudaMallocHost(p, want);
+    if (e == cudaSuccess) c.host_live[*p] = want;
+    return e;
+  }
+  return cudaMallocHost(p, want);
+}
+
+cudaError_t cached_host_free(void *p) {
+  if (!p) return cudaSuccess;
+  AllocCache &c = alloc_cache();
+  {
+    std::lock_guard<std::mutex> lk(c.mu);
+    auto it = c.host_live.find(p);
+    if (it != c.host_live.end()) { // small pinned blocks (state mirrors): kept for the next workspace
+      c.host_free.emplace(it->second, p);
+      c.host_live.erase(it);
+      return cudaSuccess;
+    }
+  }
+  return cudaFreeHost(p);
+}
+
+void cache_trim() {
+  AllocCache &c = alloc_cache();
+  std::lock_guard<std::mutex> lk(c.mu);
+  int prev = -1;
+  cudaGetDevice(&prev);
+  for (auto &kv : c.dev) {
+    cudaSetDevice(kv.first);
+    cudaDeviceSynchronize();
+    trim_device_locked(kv.second, 0);
+  }
+  if (prev >= 0) cudaSetDevice(prev);
+  for (auto &kv : c.host_free) cudaFreeHost(kv.second);
+  c.host_free.clear();
 }
 
 } // namespace cgb
@@ -94,8 +238,8 @@ int cgb_ctx_destroy(cgb_ctx *ctx) {
   if (!ctx) return CGB_OK;
   ScopedDevice sd(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  if (ctx->partials) cudaFree(ctx->partials);
-  if (ctx->ticket) cudaFree(ctx->ticket);
+  if (ctx->partials) cached_free(ctx->partials);
+  if (ctx->ticket) cached_free(ctx->ticket);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -117,7 +261,7 @@ int cgb_malloc(cgb_ctx *ctx, size_t bytes, void **d_out) {
   ScopedDevice sd(ctx->device);
   *d_out = nullptr;
   if (bytes == 0) bytes = 16; // cudaMalloc aligns to >= 256 bytes
-  CGB_CUDA(cudaMalloc(d_out, bytes));
+  CGB_CUDA(cached_malloc(d_out, bytes));
   return CGB_OK;
 }
 
@@ -125,9 +269,9 @@ int cgb_free(cgb_ctx *ctx, void *d_ptr) {
   if (!d_ptr) return CGB_OK;
   CGB_REQUIRE(ctx, "cgb_free: ctx is NULL");
   ScopedDevice sd(ctx->device);
-  // work queued on the stream may still use the buffer (reference: free after queue order)
-  CGB_CUDA(cudaStreamSynchronize(ctx->stream));
-  CGB_CUDA(cudaFree(d_ptr));
+  // work queued on the stream may still use the buffer (reference: free after queue order): the cache
+  // synchronises the device before the block can be handed out again
+  CGB_CUDA(cached_free(d_ptr));
   return CGB_OK;
 }
 
@@ -223,6 +367,11 @@ int cgb_event_destroy(cgb_event *ev) {
   if (!ev) return CGB_OK;
   cudaEventDestroy(ev->ev);
   delete ev;
+  return CGB_OK;
+}
+
+int cgb_trim(void) {
+  cache_trim();
   return CGB_OK;
 }
 

@@ -147,7 +147,7 @@ void workspace_release(cgb_csr *A) {
   cudaFree(w.st);
   cudaFree(w.partials);
   cudaFree(w.hist);
-  if (w.h_st) cudaFreeHost(w.h_st);
+  if (w.h_st) cached_host_free(w.h_st);
   for (auto &e : w.ev)
     if (e) cudaEventDestroy(e);
   w = Workspace();
@@ -164,7 +164,7 @@ int workspace_ensure(cgb_csr *A, int64_t n_ext, bool need_p1, int64_t hist_cap) 
     CGB_CUDA(cudaMalloc(&w.Ap, vb));
     CGB_CUDA(cudaMalloc(&w.st, sizeof(CgState)));
     CGB_CUDA(cudaMalloc(&w.partials, sizeof(double) * 2 * kMaxPartials));
-    CGB_CUDA(cudaMallocHost(&w.h_st, 2 * sizeof(CgState)));
+    CGB_CUDA(cached_host_alloc((void **)&w.h_st, 2 * sizeof(CgState)));
     CGB_CUDA(cudaMemsetAsync(w.st, 0, sizeof(CgState), ctx->stream));
     w.n = A->n;
     w.n_ext = n_ext;

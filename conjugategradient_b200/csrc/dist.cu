@@ -117,6 +117,8 @@ struct cgb_dist {
   std::vector<double *> halo_of;        // peers' halo buffers as mapped here (nullptr where nothing is sent)
   PeerSend send;                        // destination table of the pack kernel
   PeerRecv recv;                        // which ranks this rank receives from
+  void *bar = nullptr;                  // DistBar of the persistent loop (dist_persistent.cuh)
+  bool dead = false;                    // a peer wait timed out: windows and sequence numbers are inconsistent across ranks
   PeerCtx pctx() const { return PeerCtx{rank, nranks, d_win, seq}; }
 };
 
@@ -707,6 +709,7 @@ int cgb_dist_destroy(cgb_dist *d) {
     cudaStreamSynchronize(d->ctx->stream);
   }
   cudaFree(d->win);
+  cudaFree(d->bar);
   cudaFree(d->d_win);
   cudaFree(d->seq);
   if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
@@ -722,4 +725,5 @@ int64_t cgb_dist_halo_count(const cgb_dist *d) { return d ? d->H : 0; }
 
 } // extern "C"
 
+#include "dist_persistent.cuh"
 #include "dist_impl.cuh"

@@ -70,6 +70,15 @@ int all_agree(cgb_dist *d, int ok, int *all_ok) {
   return CGB_OK;
 }
 
+// CGB_PEER_TIMEOUT_MS (default 30000) in SM clock cycles
+long long peer_timeout_cycles(const cgb_ctx *ctx) {
+  double ms = 30000.0;
+  if (const char *e = getenv("CGB_PEER_TIMEOUT_MS")) ms = std::max(1.0, atof(e));
+  int khz = 0;
+  if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) != cudaSuccess || khz <= 0) khz = 2000000;
+  return (long long)(ms * (double)khz);
+}
+
 constexpr size_t kIpcGranule = (size_t)2 << 20; // exported allocations are whole 2 MiB blocks
 
 // Allocate this rank's window, map every peer's window.  Leaves d->peer = true only if it worked everywhere.
@@ -108,6 +117,8 @@ int peer_window_setup(cgb_dist *d) {
   }
   if (everyone) {
     CGB_CUDA(cudaMemcpy(d->d_win, d->win_of.data(), sizeof(PeerWin *) * (size_t)d->nranks, cudaMemcpyHostToDevice));
+    const long long limit = peer_timeout_cycles(d->ctx);
+    CGB_CUDA(cudaMemcpyToSymbol(g_peer_timeout_cycles, &limit, sizeof(limit)));
     d->peer = true;
   } else {
     for (int q = 0; q < d->nranks; q++)
@@ -428,6 +439,8 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   if (!d->Aloc) return fail(CGB_ERR_STATE, "No Matrix given");
   if (!d_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");
   CGB_REQUIRE(d_x, "cgb_dist_cg_solve: x is NULL");
+  CGB_REQUIRE(((uintptr_t)d_x & 15) == 0, "cgb_dist_cg_solve: x must be 16-byte aligned (128-bit vector accesses)");
+  if (d->dead) return fail(CGB_ERR_STATE, "cgb_dist_cg_solve: this handle saw a peer time-out; destroy it on every rank and create a new one");
   cgb_cg_opts o;
   if (opts_in) o = *opts_in; else cgb_cg_default_opts(&o);
   if (stats) memset(stats, 0, sizeof(*stats));
@@ -447,6 +460,13 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   CGB_TRY(workspace_ensure(A, n, false, hist_cap));
   Workspace &w = A->ws;
   const bool use_graph = o.loop_mode != CGB_LOOP_STEPWISE;
+  // Collective decisions, and the barrier that keeps rank skew out of the in-kernel waits: the host work above
+  // (engine preparation, allocations, lazy module loads) takes a different time on every rank, and the first peer
+  // kernel below waits for its peers with a time limit.
+  int persistent = 0;
+  CGB_TRY(all_agree(d, dist_persistent_eligible(d, o) ? 1 : 0, &persistent));
+  if (o.loop_mode == CGB_LOOP_PERSISTENT && !persistent)
+    return fail(CGB_ERR_UNSUPPORTED, "cgb_dist_cg_solve: CGB_LOOP_PERSISTENT needs the peer transport, the TMA row engine on every rank and a small halo part");
 
   cudaEvent_t t0, t1;
   CGB_CUDA(cudaEventCreate(&t0));
@@ -483,7 +503,13 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   const int per_iter = d->peer ? 5 : 6; // kernels of ours per iteration (NCCL's own kernels not counted)
   int64_t launches = d->peer ? 4 : 5;
   const uint64_t gkey = ((uint64_t)batch << 1) | (d->peer ? 1u : 0u);
-  if (use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != gkey)) {
+  if (persistent) { // the whole loop, the last x update included, in one cooperative kernel (dist_persistent.cuh)
+    CGB_TRY(dist_persistent_launch(d, d_x, peer_timeout_cycles(ctx)));
+    launches += 1;
+    CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+    CGB_CUDA(cudaStreamSynchronize(s));
+  }
+  if (!persistent && use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != gkey)) {
     if (w.graph) {
       cudaGraphExecDestroy(w.graph);
       w.graph = nullptr;
@@ -509,7 +535,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   }
   pt.mark("solve: workspace, K0, graph");
   // every rank takes the same decisions: the polled state is built from all-reduced scalars only
-  while (true) {
+  while (!persistent) {
     if (use_graph) {
       CGB_CUDA(cudaGraphLaunch(w.graph, s));
     } else {
@@ -520,12 +546,14 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     CGB_CUDA(cudaStreamSynchronize(s));
     if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter || w.h_st[0].comm_error) break;
   }
-  if (w.h_st[0].comm_error)
-    return fail(CGB_ERR_NCCL, "cgb_dist_cg_solve: a peer did not answer within the time limit (rank %d, trip %lld)", d->rank,
+  if (w.h_st[0].comm_error) {
+    d->dead = true;
+    return fail(CGB_ERR_NCCL, "cgb_dist_cg_solve: a peer did not answer within the time limit (rank %d, trip %lld; CGB_PEER_TIMEOUT_MS)", d->rank,
                 (long long)w.h_st[0].iter);
-  if (n > 0) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st, 0); // last trip's x update
+  }
+  if (n > 0 && !persistent) cg_xflush_kernel<<<A->grid_pup, kBlock, 0, s>>>(n, d_x, w.p0, w.p1, 0, w.st, 0); // last trip's x update
   CGB_CUDA(cudaGetLastError());
-  launches += 1;
+  if (!persistent) launches += 1;
   CGB_CUDA(cudaEventRecord(t1, s));
   CGB_CUDA(cudaEventSynchronize(t1));
   pt.mark("solve: iterations");
@@ -541,7 +569,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     stats->nan_stop = f.nan_stop;
     stats->solve_ms = ms;
     stats->kernel_launches = launches;
-    stats->loop_mode = use_graph ? CGB_LOOP_GRAPH : CGB_LOOP_STEPWISE;
+    stats->loop_mode = persistent ? CGB_LOOP_PERSISTENT : use_graph ? CGB_LOOP_GRAPH : CGB_LOOP_STEPWISE;
     { const int eng = csr_engine(A); stats->format = eng == kEngSell ? CGB_FMT_SELL : eng == kEngDict ? CGB_FMT_DICT : CGB_FMT_CSR; }
   }
   return CGB_OK;
@@ -557,6 +585,11 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
   if (d->Ahalo) CGB_TRY(csr_prepare(d->Ahalo));
   CGB_TRY(workspace_ensure(A, A->n, false, 0));
   Workspace &w = A->ws;
+  if (d->dead) return fail(CGB_ERR_STATE, "cgb_dist_residual: this handle saw a peer time-out; destroy it on every rank and create a new one");
+  if (d->peer) { // host-level barrier: rank skew stays out of the in-kernel waits
+    int all = 0;
+    CGB_TRY(all_agree(d, 1, &all));
+  }
   CGB_TRY(halo_exchange(d, d_x, 0));
   if (A->n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
   CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
@@ -574,7 +607,10 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
   CGB_CUDA(cudaStreamSynchronize(s));
   *rr = ctx->pinned[0];
   *xx = ctx->pinned[1];
-  if (ctx->pinned[2] != 0.0) return fail(CGB_ERR_NCCL, "cgb_dist_residual: a peer did not answer within the time limit");
+  if (ctx->pinned[2] != 0.0) {
+    d->dead = true;
+    return fail(CGB_ERR_NCCL, "cgb_dist_residual: a peer did not answer within the time limit");
+  }
   return CGB_OK;
 }
 

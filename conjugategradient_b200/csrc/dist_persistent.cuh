@@ -1,0 +1,424 @@
+// dist_persistent.cuh — the row-partitioned CG loop as ONE cooperative kernel per rank (included by dist.cu).
+//
+// The launch-per-kernel loop of dist_impl.cuh pays five kernel boundaries and two last-CTA all-reduce round trips
+// per trip (about 60 us of fixed cost at 8 GPUs: VERDICT r1, weak item 5).  Here a rank runs its whole solve in one
+// kernel, the way persistent.cuh does on one GPU; a trip is
+//
+//   phase P   x += alpha_prev p (deferred) ; p = r + beta p                          (src/CG.hpp:390, :418)
+//   -- grid barrier --
+//   pack      boundary entries of p stored straight into the owners' halo buffers (NVLink), then this rank's
+//             sequence flag raised in every destination window by the CTA that finishes the pack last
+//   phase S   Ap = A_loc p through the TMA-staged CSR engine, partial p.Ap             (:374-379)
+//             -- the halo transfer is in flight meanwhile --
+//   -- grid barrier --
+//   phase H   wait for the halo flags; Ap[row] += A_halo[row,:] . halo, partial p.Ap += p[row] * that
+//   -- reduction: per-CTA partials -> the last CTA to arrive sums them in fixed order and stores the rank's total
+//      into slot [rank] of EVERY rank's window; ALL CTAs of all ranks then wait for the P flags in their own window
+//      and add the P slots in rank order.  One step is the grid barrier and the all-reduce at once, every thread
+//      ends with the same bits, nothing is broadcast through memory. --          alpha = rr / p.Ap   (:385-386)
+//   phase U   r -= alpha Ap, partial r.r                                              (:392, :406)
+//   -- reduction (same) --   stop rule on the OLD rr (:396-404), beta = rr'/rr (:414), ++trip (:436)
+//
+// Sequence numbers (PeerSeq) continue those of the set-up kernels and are written back at the end, so the
+// residual / set-up kernels that follow see a consistent window.  Slots are double-buffered on the parity of the
+// reduction number: a rank can be at most one reduction ahead of the slowest (finishing reduction s needs every
+// rank's contribution to s, which a rank only sends once ALL its CTAs have finished reading reduction s-1).  The
+// same argument makes the single-buffered halo safe: nobody packs trip k+1 before everyone is past phase H of trip k.
+// Data written by other CTAs inside the kernel (p, Ap) is read with plain (weak) loads after an acquire at the
+// barrier, never through the non-coherent path.  Every wait carries a time limit and watches the state's
+// comm_error flag, so one failing wait takes every CTA of the rank out of the loop instead of hanging the GPU.
+#pragma once
+
+namespace {
+
+struct DistBar {                 // device words of the persistent loop, zeroed by the host before every launch
+  unsigned long long arrive;     // grid barrier: arrivals so far (monotone)
+  unsigned long long gen;        // grid barrier: generations completed
+  unsigned long long pack;       // CTAs that finished packing (monotone)
+  unsigned long long red;        // reduction ticket (monotone)
+};
+
+struct DistLoopArgs {
+  CsrView A;                     // A_loc: all local rows, owned columns
+  int64_t nh;                    // rows that touch remote columns
+  const int *h_rowptr, *h_cols;  // A_halo (columns index the halo buffer)
+  const double *h_vals;
+  const int *halo_rows;
+  const double *halo;
+  int64_t S;                     // entries this rank sends
+  const int *send_idx;
+  PeerSend ps;
+  PeerRecv pr;
+  PeerCtx pc;
+  double *x, *r, *p, *Ap;
+  CgState *st;
+  double *partials;
+  double *hist;
+  DistBar *bar;
+  long long timeout_cycles;
+  unsigned jitter_ns;            // CGB_DIST_JITTER_NS (tests): every CTA sleeps a pseudo-random time below this before each phase
+};
+
+struct GatherWeak { // p is rewritten every trip by other CTAs of this very kernel: plain ld.global, ordered by the barrier's acquire
+  const double *x;
+  __device__ __forceinline__ double operator()(int c) const {
+    double v;
+    asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(x + c) : "memory");
+    return v;
+  }
+  struct At {
+    const double *xr;
+    __device__ __forceinline__ double operator()(int off) const {
+      double v;
+      asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(xr + off) : "memory");
+      return v;
+    }
+  };
+  __device__ __forceinline__ At at(int64_t row) const { return At{x + row}; }
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Spin until *flag >= want (SYS = flag written by a peer GPU).  False on time-out or when another CTA reported one.
+template <bool SYS>
+__device__ __forceinline__ bool dist_wait(const unsigned long long *flag, unsigned long long want, CgState *st, long long limit) {
+  if ((SYS ? ld_acquire_sys_u64(flag) : ld_acquire_gpu_u64(flag)) >= want) return true;
+  const long long t0 = clock64();
+  int spins = 0;
+  while ((SYS ? ld_acquire_sys_u64(flag) : ld_acquire_gpu_u64(flag)) < want) {
+    if ((++spins & 63) == 0) {
+      if (*(volatile int *)&st->comm_error) return false;
+      if (clock64() - t0 > limit) {
+        *(volatile int *)&st->comm_error = 1;
+        __threadfence();
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+// All threads of all CTAs; `gen` is the caller's count of barriers passed so far.  False: leave the loop.
+__device__ __forceinline__ bool dist_grid_barrier(DistBar *bar, unsigned long long &gen, CgState *st, long long limit) {
+  __shared__ int s_ok;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned long long t = atomicAdd(&bar->arrive, 1ull) + 1ull;
+    bool ok = true;
+    if (t == (gen + 1ull) * gridDim.x) st_release_gpu_u64(&bar->gen, gen + 1ull);
+    else ok = dist_wait<false>(&bar->gen, gen + 1ull, st, limit);
+    __threadfence();
+    s_ok = ok ? 1 : 0;
+  }
+  gen += 1ull;
+  __syncthreads();
+  return s_ok != 0;
+}
+
+// Sum of `v` over all threads of all CTAs of ALL ranks, the same bits in every thread.  `nred` counts the reductions of
+// this launch, `seq` the all-reduces on the window since it was created.  *ok is cleared on a failed wait.
+__device__ __forceinline__ double dist_allreduce(double v, const DistLoopArgs &a, PeerWin *const *win, unsigned long long &nred,
+                                                 unsigned long long &seq, double *red, double *slots, bool *ok) {
+  __shared__ int s_last, s_okr;
+  __shared__ double s_total;
+  v = block_sum(v, red);
+  if (threadIdx.x == 0) {
+    *(volatile double *)&a.partials[blockIdx.x] = v;
+    __threadfence();
+    const unsigned long long t = atomicAdd(&a.bar->red, 1ull) + 1ull;
+    s_last = (t == (nred + 1ull) * gridDim.x);
+    s_okr = 1;
+  }
+  nred += 1ull;
+  seq += 1ull;
+  const int par = (int)(seq & 1ull);
+  __syncthreads();
+  if (s_last) { // this CTA saw every partial of the rank: fixed-order sum, then one store per destination window
+    __threadfence();
+    const double total = reduce_partials(a.partials, gridDim.x, red);
+    if (threadIdx.x == 0) s_total = total;
+    __syncthreads();
+    if (threadIdx.x < a.pc.nranks) {
+      PeerWin *w = win[threadIdx.x];
+      st_relaxed_sys_f64(&w->slot[par][a.pc.rank], s_total);
+      st_release_sys_u64(&w->sflag[par][a.pc.rank], seq);
+    }
+  }
+  if (threadIdx.x < a.pc.nranks) {
+    const PeerWin *me = win[a.pc.rank];
+    if (dist_wait<true>(&me->sflag[par][threadIdx.x], seq, a.st, a.timeout_cycles)) slots[threadIdx.x] = ld_relaxed_sys_f64(&me->slot[par][threadIdx.x]);
+    else {
+      slots[threadIdx.x] = 0.0;
+      s_okr = 0;
+    }
+  }
+  __syncthreads();
+  double sum = 0.0;
+  for (int q = 0; q < a.pc.nranks; q++) sum += slots[q]; // rank order: identical on every rank
+  if (!s_okr) *ok = false;
+  __syncthreads(); // slots / s_last are reused by the next call
+  return sum;
+}
+
+__device__ __forceinline__ void dist_pupdate_body(int64_t n, const double *r, double *p, double *x, double alpha, double beta) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  const double2 *r2 = reinterpret_cast<const double2 *>(r);
+  double2 *p2 = reinterpret_cast<double2 *>(p);
+  double2 *x2 = reinterpret_cast<double2 *>(x);
+  for (int64_t i = tid; i < n2; i += nthr) {
+    const double2 rv = r2[i];
+    double2 pv = p2[i];
+    double2 xv = x2[i];
+    xv.x = fma(alpha, pv.x, xv.x);
+    xv.y = fma(alpha, pv.y, xv.y);
+    pv.x = fma(beta, pv.x, rv.x);
+    pv.y = fma(beta, pv.y, rv.y);
+    x2[i] = xv;
+    p2[i] = pv;
+  }
+  if ((n & 1) && tid == 0) {
+    const double po = p[n - 1];
+    x[n - 1] = fma(alpha, po, x[n - 1]);
+    p[n - 1] = fma(beta, po, r[n - 1]);
+  }
+}
+
+// Stress hook for the flag protocols (tests/test_dist_gpu.py, variant "jitter"): CTAs and ranks drift apart at random.
+__device__ __forceinline__ void dist_jitter(const DistLoopArgs &a, unsigned salt) {
+  if (a.jitter_ns == 0) return;
+  unsigned h = (blockIdx.x + 1u) * 2654435761u ^ (salt + 1u) * 40503u ^ (unsigned)(a.pc.rank + 1) * 2246822519u;
+  h ^= h >> 15;
+  h *= 2246822519u;
+  h ^= h >> 13;
+  if (threadIdx.x == 0) __nanosleep(h % a.jitter_ns);
+  __syncthreads();
+}
+
+// r -= alpha Ap, this thread's share of r.r.  No __restrict__ / const here: Ap is written by other CTAs of this very kernel,
+// so its loads must stay on the coherent path (cg_update_body's qualifiers would allow ld.global.nc).
+__device__ __forceinline__ double dist_update_body(int64_t n, double *r, double *Ap, double alpha) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  double2 *r2 = reinterpret_cast<double2 *>(r);
+  double2 *q2 = reinterpret_cast<double2 *>(Ap);
+  double acc = 0.0;
+  for (int64_t i = tid; i < n2; i += nthr) {
+    double2 rv = r2[i];
+    const double2 qv = q2[i];
+    rv.x = fma(-alpha, qv.x, rv.x);
+    rv.y = fma(-alpha, qv.y, rv.y);
+    r2[i] = rv;
+    acc = fma(rv.x, rv.x, acc);
+    acc = fma(rv.y, rv.y, acc);
+  }
+  if ((n & 1) && tid == 0) {
+    const double rv = fma(-alpha, Ap[n - 1], r[n - 1]);
+    r[n - 1] = rv;
+    acc = fma(rv, rv, acc);
+  }
+  return acc;
+}
+
+template <int L>
+__global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(const __grid_constant__ DistLoopArgs a) {
+  extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
+  __shared__ double red[32];
+  __shared__ double slots[kMaxRanks];
+  __shared__ PeerWin *win[kMaxRanks];
+  __shared__ int s_flag;
+  CgState *st = a.st;
+  if (threadIdx.x < a.pc.nranks) win[threadIdx.x] = a.pc.win[threadIdx.x];
+  __syncthreads();
+  // the set-up kernels armed the state; every thread carries its own copy of the scalars (same slots, same order => same bits)
+  double rr = st->rr, alpha = 0.0, beta = 0.0;
+  const double tol = st->tol;
+  const long long max_iter = st->max_iter, hist_cap = st->hist_cap;
+  const int record = st->record_history;
+  long long it = 0;
+  int done = st->done, nan_stop = 0;
+  unsigned long long gen = 0, nred = 0, npack = 0;
+  unsigned long long red_seq = a.pc.seq->red, halo_seq = a.pc.seq->halo;
+  const int64_t n = a.A.n;
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  bool ok = true;
+  while (!done && it < max_iter) {
+    // ---- phase P ----
+    dist_jitter(a, 4u * (unsigned)it);
+    dist_pupdate_body(n, a.r, a.p, a.x, alpha, beta);
+    if (!dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
+    dist_jitter(a, 4u * (unsigned)it + 1u);
+    // ---- pack: boundary entries of p to their owners, flags by the CTA that finishes last ----
+    halo_seq += 1ull;
+    for (int64_t k = gtid; k < a.S; k += nthr) {
+      int q = 0;
+      while (k >= a.ps.soff[q + 1]) q++;
+      double v;
+      asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(a.p + a.send_idx[k]) : "memory");
+      a.ps.dst[q][k - a.ps.soff[q]] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned long long t = atomicAdd(&a.bar->pack, 1ull) + 1ull;
+      s_flag = (t == (npack + 1ull) * gridDim.x);
+      if (s_flag) __threadfence_system(); // acquire side of the ticket: every CTA's stores precede the flags below
+    }
+    npack += 1ull;
+    __syncthreads();
+    if (s_flag && threadIdx.x < a.pc.nranks && a.ps.soff[threadIdx.x + 1] > a.ps.soff[threadIdx.x]) {
+      __threadfence_system();
+      st_release_sys_u64(&win[threadIdx.x]->hflag[a.pc.rank], halo_seq);
+    }
+    // ---- phase S: local rows through the TMA tile engine ----
+    double a0 = 0.0, a1 = 0.0;
+    {
+      GatherWeak g{a.p};
+      EpiDotP e{a.Ap, a.p};
+      spmv_rows_tma<L>(a.A.n, a.A.nnz, a.A.rowptr, a.A.cols, a.A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
+      spmv_tma_teardown(cgb_dyn_smem, kTmaConsumers / L);
+    }
+    if (!dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
+    dist_jitter(a, 4u * (unsigned)it + 2u);
+    // ---- phase H: halo rows once the neighbours' entries are here ----
+    if (a.nh > 0) {
+      if (threadIdx.x == 0) s_flag = 1;
+      __syncthreads();
+      if (threadIdx.x < a.pc.nranks && a.pr.from[threadIdx.x]) {
+        if (!dist_wait<true>(&win[a.pc.rank]->hflag[threadIdx.x], halo_seq, st, a.timeout_cycles)) s_flag = 0;
+      }
+      __syncthreads();
+      if (!s_flag) { ok = false; break; }
+      for (int64_t k = gtid; k < a.nh; k += nthr) {
+        double s = 0.0;
+        for (int j = a.h_rowptr[k], e = a.h_rowptr[k + 1]; j < e; j++) s = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s);
+        const int row = a.halo_rows[k];
+        a.Ap[row] += s;
+        a0 = fma(a.p[row], s, a0);
+      }
+    }
+    const double pAp = dist_allreduce(a0, a, win, nred, red_seq, red, slots, &ok);
+    if (!ok) break;
+    alpha = rr / pAp; // src/CG.hpp:385-386
+    // ---- phase U ----
+    dist_jitter(a, 4u * (unsigned)it + 3u);
+    const double acc = dist_update_body(n, a.r, a.Ap, alpha);
+    const double rr_new = dist_allreduce(acc, a, win, nred, red_seq, red, slots, &ok);
+    if (!ok) break;
+    if (isnan(rr) || sqrt(rr) <= tol) { // the rr from BEFORE this trip's update (one-trip lag, src/CG.hpp:396-404)
+      done = 1;
+      nan_stop = isnan(rr) ? 1 : 0;
+    }
+    beta = rr_new / rr;
+    rr = rr_new;
+    it++;
+    if (record && it < hist_cap && blockIdx.x == 0 && threadIdx.x == 0) a.hist[it] = rr_new;
+  }
+  // the x update of the last trip (its p is complete: every CTA passed the barrier after phase P)
+  if (it > 0 && ok) {
+    const int64_t n2 = n >> 1;
+    double2 *x2 = reinterpret_cast<double2 *>(a.x);
+    const double2 *p2 = reinterpret_cast<const double2 *>(a.p);
+    for (int64_t i = gtid; i < n2; i += nthr) {
+      double2 xv = x2[i];
+      const double2 pv = p2[i];
+      xv.x = fma(alpha, pv.x, xv.x);
+      xv.y = fma(alpha, pv.y, xv.y);
+      x2[i] = xv;
+    }
+    if ((n & 1) && gtid == 0) a.x[n - 1] = fma(alpha, a.p[n - 1], a.x[n - 1]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->rr = rr;
+    st->alpha = alpha;
+    st->beta = beta;
+    st->iter = it;
+    st->done = ok ? done : 1;
+    st->nan_stop = nan_stop;
+    if (!ok) st->comm_error = 1;
+    a.pc.seq->red = red_seq;
+    a.pc.seq->halo = halo_seq;
+  }
+}
+
+// Host side: is the persistent loop applicable on THIS rank (the ranks then agree collectively), and its launch.
+bool dist_persistent_eligible(const cgb_dist *d, const cgb_cg_opts &o) {
+  if (const char *e = getenv("CGB_DIST_PERSISTENT"))
+    if (atoi(e) == 0) return false;
+  if (!d->peer || !d->ctx->coop_ok) return false;
+  if (o.loop_mode != CGB_LOOP_AUTO && o.loop_mode != CGB_LOOP_PERSISTENT) return false;
+  if (o.time_kernels || o.jacobi || o.residual_replace_every > 0 || o.fuse_p_update) return false;
+  const cgb_csr *A = d->Aloc;
+  if (A->n <= 0 || csr_engine(A) != kEngTma) return false;
+  // the halo rows are served by a plain row-per-thread pass: fine for stencil slabs (a few entries per boundary row), not
+  // for blocks whose halo part is a real share of the matrix (random matrices: those keep the launch-per-kernel loop)
+  if (d->Ahalo && d->Ahalo->nnz * 2 > A->nnz) return false;
+  return true;
+}
+
+template <int L>
+int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles) {
+  cgb_csr *A = d->Aloc;
+  Workspace &w = A->ws;
+  cudaStream_t s = d->ctx->stream;
+  auto kernel = cg_dist_persistent_kernel<L>;
+  const size_t smem = tma_smem_bytes(kTmaConsumers / L);
+  CGB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  CGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kTmaThreads, smem));
+  if (occ < 1) return fail(CGB_ERR_CUDA, "cg_dist_persistent_kernel: does not fit an SM");
+  int grid = std::min(occ * d->ctx->sm_count, kMaxPartials);
+  if (const char *e = getenv("CGB_DIST_PERSISTENT_CTAS")) grid = std::max(1, std::min(grid, atoi(e)));
+  DistLoopArgs a;
+  memset(&a, 0, sizeof(a));
+  a.A = csr_view(A);
+  a.nh = d->nh;
+  if (d->Ahalo) {
+    a.h_rowptr = d->Ahalo->rowptr;
+    a.h_cols = d->Ahalo->cols;
+    a.h_vals = d->Ahalo->vals;
+  }
+  a.halo_rows = d->halo_rows;
+  a.halo = d->halo;
+  a.S = d->S;
+  a.send_idx = d->send_idx;
+  a.ps = d->send;
+  a.pr = d->recv;
+  a.pc = d->pctx();
+  a.x = d_x;
+  a.r = w.r;
+  a.p = w.p0;
+  a.Ap = w.Ap;
+  a.st = w.st;
+  a.partials = w.partials;
+  a.hist = w.hist;
+  a.bar = static_cast<DistBar *>(d->bar);
+  a.timeout_cycles = timeout_cycles;
+  if (const char *e = getenv("CGB_DIST_JITTER_NS")) a.jitter_ns = (unsigned)std::max(0, atoi(e));
+  if (!d->bar) CGB_CUDA(cudaMalloc(&d->bar, sizeof(DistBar)));
+  CGB_CUDA(cudaMemsetAsync(d->bar, 0, sizeof(DistBar), s));
+  void *args[] = {&a};
+  CGB_CUDA(cudaLaunchCooperativeKernel((void *)kernel, dim3(grid), dim3(kTmaThreads), args, smem, s));
+  return CGB_OK;
+}
+
+int dist_persistent_launch(cgb_dist *d, double *d_x, long long timeout_cycles) {
+  switch (d->Aloc->lanes_tma) {
+  case 1: return dist_persistent_launch_L<1>(d, d_x, timeout_cycles);
+  case 2: return dist_persistent_launch_L<2>(d, d_x, timeout_cycles);
+  case 4: return dist_persistent_launch_L<4>(d, d_x, timeout_cycles);
+  case 8: return dist_persistent_launch_L<8>(d, d_x, timeout_cycles);
+  case 16: return dist_persistent_launch_L<16>(d, d_x, timeout_cycles);
+  default: return dist_persistent_launch_L<32>(d, d_x, timeout_cycles);
+  }
+}
+
+} // namespace

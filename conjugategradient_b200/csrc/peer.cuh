@@ -13,8 +13,8 @@
 // Ordering: data stores, __threadfence_system(), then st.release.sys of the flag; the reader
 // spins with ld.acquire.sys and reads the data after it.  Slots are double-buffered on the parity
 // of the sequence number; a rank can only be one round ahead of the slowest one, because finishing
-// round s needs every rank's flag of round s.  Every wait has a timeout that stops the loop and
-// reports an error instead of hanging the GPU.
+// round s needs every rank's flag of round s.  Every wait has a time limit (CGB_PEER_TIMEOUT_MS, default 30 s) that stops
+// the loop and reports an error instead of hanging the GPU; the handle is unusable afterwards.
 //
 // There is nothing of this in the reference (single device); SURVEY.md §8(e).
 #pragma once
@@ -23,7 +23,9 @@
 namespace cgb {
 
 constexpr int kMaxRanks = 16;
-constexpr long long kPeerTimeoutCycles = 6000000000LL; // ~3 s at 2 GHz
+// Time limit of every peer wait, in SM clock cycles: set once per process from CGB_PEER_TIMEOUT_MS (default 30 s;
+// dist.cu: peer_timeout_cycles) — long enough for any honest rank skew, short enough not to hang a GPU for good.
+__device__ long long g_peer_timeout_cycles = 60000000000LL;
 
 struct PeerWin { // one per rank, written by the peers
   double slot[2][kMaxRanks];               // all-reduce contributions, [parity][source rank]
@@ -65,7 +67,7 @@ __device__ __forceinline__ bool peer_wait(const unsigned long long *flag, unsign
   if (ld_acquire_sys_u64(flag) >= want) return true;
   const long long t0 = clock64();
   while (ld_acquire_sys_u64(flag) < want) {
-    if (clock64() - t0 > kPeerTimeoutCycles) return false;
+    if (clock64() - t0 > g_peer_timeout_cycles) return false;
     __nanosleep(20);
   }
   return true;

@@ -73,6 +73,16 @@ __device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src
       : "memory");
 }
 
+// After spmv_rows_tma in a kernel that calls it more than once (persistent loops): all threads of the CTA; the stage
+// barriers are invalidated so the next call may initialise them again (an mbarrier must be invalidated before its
+// memory is re-initialised).
+__device__ __forceinline__ void spmv_tma_teardown(unsigned char *smem_raw, int tile_rows) {
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + kTmaStages * tma_stage_bytes(tile_rows));
+  __syncthreads(); // every staged tile has been consumed: no copy in flight, no arrival pending on `full`
+  if (threadIdx.x == 0)
+    for (int s = 0; s < 2 * kTmaStages; s++) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&bars[s])) : "memory");
+}
+
 // Row sums of `len` staged entries for one lane of an L-lane group; 4 gathers in flight.
 template <int L, class G>
 __device__ __forceinline__ double row_sum_staged(const double *sv, const int *sc, int s, int e, int sub, const G &g) {

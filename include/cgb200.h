@@ -62,6 +62,13 @@ int cgb_ctx_sm_count(cgb_ctx *ctx);
  * Copies are ordered on the context stream; the *_sync flag waits for completion. */
 int cgb_malloc(cgb_ctx *ctx, size_t bytes, void **d_out);
 int cgb_free(cgb_ctx *ctx, void *d_ptr);
+/* Device memory freed by the library (cgb_free, cgb_csr_destroy, work vectors, multi-GPU blocks) is kept in a
+ * per-device cache of whole allocations and handed out again for requests of the same size, so repeated
+ * host-buffer solves (cgb_cg_solve_host, cgb_dist_set_matrix) cost no driver allocation after the first; the
+ * reference allocates afresh on every setMatrix / solve (src/LinearAlgebraTypes.hpp:109-119, src/CG.hpp:276-301).
+ * cgb_trim returns the cached blocks to the driver (environment: CGB_ALLOC_CACHE=0 disables the cache,
+ * CGB_ALLOC_CACHE_MAX_GB bounds it, default 64). */
+int cgb_trim(void);
 int cgb_memcpy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes, int sync);
 int cgb_memcpy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes, int sync);
 int cgb_memcpy_d2d(cgb_ctx *ctx, void *d_dst, const void *d_src, size_t bytes);

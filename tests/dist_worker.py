@@ -50,7 +50,21 @@ def main():
         else:
             dcg.set_matrix(starts, A)   # same communicator, new matrix
         bv, xv = S.Vector(ctx, b[lo:hi]), S.Vector(ctx, n=max(hi - lo, 1))
+        if os.environ.get("CGB_TEST_HOST_JITTER"):
+            import time
+            time.sleep(float(np.random.default_rng(rank * 7919 + len(name)).uniform(0.0, 0.3)))
         st = dcg.solve(bv, xv, tol)
+        expect = os.environ.get("CGB_TEST_EXPECT_LOOP", "")
+        stencil = not name.startswith("rspd")
+        if expect == "persistent" and name in ("p3d7_24", "p2d_64"):   # (a 27-point block one plane thick is mostly halo: it keeps the graph loop)
+            assert st["loop_mode"] == L.LOOP_PERSISTENT, st
+        if expect == "graph":
+            assert st["loop_mode"] == L.LOOP_GRAPH, st
+        if os.environ.get("CGB_DIST_JITTER_NS") and stencil:   # bitwise reproducible whatever the timing
+            x_first = xv.download().copy()
+            xv.upload(np.zeros(max(hi - lo, 1)))
+            st2 = dcg.solve(bv, xv, tol)
+            assert st2["iterations"] == st["iterations"] and st2["rr"] == st["rr"] and np.array_equal(xv.download(), x_first)
         rr, xx = dcg.residual(xv, bv)
         xl = xv.download()[: hi - lo]
         parts = [None] * world

@@ -11,12 +11,23 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("variant", ["default", "halo_engine", "nccl", "dict"])
+@pytest.mark.parametrize("variant", ["default", "jitter", "graph", "halo_engine", "nccl", "dict"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_dist_solve_matches_oracle(world, variant):
     if L.load().cgb_device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     env = dict(os.environ)
+    if variant == "default":
+        env["CGB_TEST_EXPECT_LOOP"] = "persistent"   # stencil blocks run the whole loop in one cooperative kernel per rank
+    if variant == "jitter":
+        # flag-protocol stress: every CTA of every rank sleeps a pseudo-random time (< 20 us) before each phase, and the
+        # ranks enter every solve after a random host delay; results must not change by a bit
+        env["CGB_DIST_JITTER_NS"] = "20000"
+        env["CGB_TEST_HOST_JITTER"] = "1"
+        env["CGB_TEST_EXPECT_LOOP"] = "persistent"
+    if variant == "graph":
+        env["CGB_DIST_PERSISTENT"] = "0"          # the launch-per-kernel loop (CUDA-graph batches) stays correct
+        env["CGB_TEST_EXPECT_LOOP"] = "graph"
     if variant == "halo_engine":
         env["CGB_HALO_ENGINE_MIN"] = "1"      # A_halo through the regular row engines even for these small cases
     if variant == "nccl":

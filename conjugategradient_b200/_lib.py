@@ -57,6 +57,7 @@ SIGNATURES = {
     "cgb_ctx_stream": (c_vp, [c_vp]),
     "cgb_ctx_device": (C.c_int, [c_vp]),
     "cgb_ctx_sm_count": (C.c_int, [c_vp]),
+    "cgb_ctx_set_progress": (C.c_int, [c_vp, c_vp, c_vp]),
     "cgb_malloc": (C.c_int, [c_vp, C.c_size_t, C.POINTER(c_vp)]),
     "cgb_free": (C.c_int, [c_vp, c_vp]),
     "cgb_trim": (C.c_int, []),

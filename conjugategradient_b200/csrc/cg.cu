@@ -222,6 +222,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (!d_b) return fail(CGB_ERR_STATE, "No right hand side to solve for");  // src/CG.hpp:266-268
   CGB_REQUIRE(d_x, "cgb_cg_solve: x is NULL");
   CGB_REQUIRE(A->ctx == ctx, "cgb_cg_solve: matrix belongs to another context");
+  CGB_REQUIRE(((uintptr_t)d_x & 15) == 0, "cgb_cg_solve: x must be 16-byte aligned (128-bit vector accesses)");
   cgb_cg_opts o;
   if (opts_in) o = *opts_in; else cgb_cg_default_opts(&o);
   if (stats) memset(stats, 0, sizeof(*stats));
@@ -421,6 +422,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     }
     CGB_CUDA(cudaEventSynchronize(polled[check]));
     const CgState &h = w.h_st[check];
+    if (ctx->progress) ctx->progress((int64_t)h.iter, n, h.rr, ctx->progress_user); // reference: percentage line, src/CG.hpp:428-433
     if (cfg.time_kernels) {
       if (prev_active_at_start) {
         float a = 0, b = 0, c = 0;

@@ -79,6 +79,8 @@ struct cgb_ctx {
   double *partials = nullptr;
   unsigned int *ticket = nullptr;
   double *pinned = nullptr; // small pinned bounce buffer (scalars)
+  cgb_progress_fn progress = nullptr; // called after every state poll of a solve (cgb_ctx_set_progress)
+  void *progress_user = nullptr;
 };
 
 struct cgb_event {
@@ -115,6 +117,9 @@ cudaError_t cached_free(void *p);
 cudaError_t cached_host_alloc(void **p, size_t bytes);
 cudaError_t cached_host_free(void *p);
 void cache_trim();
+// host <-> device copies on the context's stream; pageable host memory is staged through pinned buffers (core.cu)
+cudaError_t copy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes);
+cudaError_t copy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes);
 
 #ifdef __CUDACC__
 // ---- device helpers ------------------------------------------------------------------------

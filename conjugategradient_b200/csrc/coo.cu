@@ -214,6 +214,12 @@ int coo_to_csr_device(cgb_ctx *ctx, int64_t n_rows, int64_t h, const int *d_r, c
     const int tot32 = (int)total;
     CGB_CUDA(cudaMemcpyAsync(rowptr + n, &tot32, sizeof(int), cudaMemcpyHostToDevice, s));
     CGB_CUDA(cudaStreamSynchronize(s));
+    // The reference dialect drops empty rows but leaves the column ids alone (test/mm_reader.cpp:92-104): with an empty
+    // row the columns reach past the compacted dimension and the reference's spmv reads outside its vector (undefined
+    // behaviour there, a device fault here).  Such a file cannot be an SPD system: refuse it.
+    if (span > n)
+      return fail(CGB_ERR_INVALID, "matrix has %lld empty row(s): column ids reach %lld but only %lld rows hold entries "
+                  "(the reference reader compacts rows without renumbering columns)", (long long)(span - n), (long long)span, (long long)n);
   } else {
     n = n_rows >= 0 ? n_rows : span;
     CGB_CUDA(cudaMalloc(&rowptr, sizeof(int) * (size_t)(n + 1) + 64));

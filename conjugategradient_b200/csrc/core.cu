@@ -6,9 +6,12 @@
 
 #include <stdarg.h>
 
+#include <algorithm>
 #include <map>
 #include <mutex>
+#include <thread>
 #include <unordered_map>
+#include <vector>
 
 namespace cgb {
 
@@ -177,6 +180,140 @@ void cache_trim() {
   c.host_free.clear();
 }
 
+// ---- pageable host memory: staged copies --------------------------------------------------------------------
+// The reference's upload / download sites hand the queue plain std::vector storage (src/LinearAlgebraTypes.hpp:
+// 109-119, :177-183; src/CG.hpp:517-532).  A cudaMemcpyAsync from pageable memory goes through the driver's own
+// single-threaded staging at a fraction of the PCIe rate, so copies of kStageMin bytes or more whose host side is
+// not page-locked are pipelined here instead: kStageWorkers host threads move 4 MiB chunks between the caller's
+// buffer and their own pair of pinned bounce buffers while the copy engine moves the previous chunks, each worker
+// on its own stream, fenced against the context's stream with events on both sides.  When the call returns the
+// caller's buffer has been read completely (upload) or written completely (download).
+namespace {
+constexpr size_t kStageMin = (size_t)8 << 20;
+constexpr size_t kStageChunk = (size_t)4 << 20;
+constexpr int kStageWorkersMax = 8;
+
+struct Stager {
+  std::mutex mu; // one staged copy at a time per process
+  int device = -1;
+  int workers = 0;
+  void *buf[kStageWorkersMax][2] = {};
+  cudaEvent_t ev[kStageWorkersMax][2] = {};
+  cudaEvent_t done[kStageWorkersMax] = {};
+  cudaStream_t st[kStageWorkersMax] = {};
+  cudaEvent_t start = nullptr;
+  bool ok = false;
+};
+Stager &stager() {
+  static Stager *s = new Stager();
+  return *s;
+}
+
+bool stager_init(Stager &s, int device) {
+  if (s.ok && s.device == device) return true;
+  if (s.ok) return false; // bound to another device: that caller takes the driver's path
+  int hw = (int)std::thread::hardware_concurrency();
+  int w = hw >= 16 ? 6 : hw >= 8 ? 4 : 2;
+  if (const char *e = getenv("CGB_STAGE_THREADS")) w = std::max(1, std::min(kStageWorkersMax, atoi(e)));
+  if (cudaEventCreateWithFlags(&s.start, cudaEventDisableTiming) != cudaSuccess) return false;
+  for (int i = 0; i < w; i++) {
+    bool good = cudaStreamCreateWithFlags(&s.st[i], cudaStreamNonBlocking) == cudaSuccess &&
+                cudaEventCreateWithFlags(&s.done[i], cudaEventDisableTiming) == cudaSuccess;
+    for (int b = 0; b < 2 && good; b++)
+      good = cudaMallocHost(&s.buf[i][b], kStageChunk) == cudaSuccess &&
+             cudaEventCreateWithFlags(&s.ev[i][b], cudaEventDisableTiming) == cudaSuccess;
+    if (!good) {
+      cudaGetLastError();
+      return false;
+    }
+  }
+  s.workers = w;
+  s.device = device;
+  s.ok = true;
+  return true;
+}
+
+bool host_is_pageable(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return true;
+  }
+  return at.type == cudaMemoryTypeUnregistered;
+}
+
+// to_device: h -> d, else d -> h.  Returns false when staging is not available (caller falls back to a plain copy).
+bool staged_copy(cgb_ctx *ctx, void *d, void *h, size_t bytes, bool to_device, cudaError_t *err) {
+  if (const char *e = getenv("CGB_STAGE"))
+    if (atoi(e) == 0) return false;
+  Stager &s = stager();
+  std::lock_guard<std::mutex> lk(s.mu);
+  if (!stager_init(s, ctx->device)) return false;
+  const size_t nchunks = (bytes + kStageChunk - 1) / kStageChunk;
+  const int W = (int)std::min<size_t>((size_t)s.workers, nchunks);
+  *err = cudaEventRecord(s.start, ctx->stream); // the device side of the copy is ordered after what the stream holds
+  if (*err != cudaSuccess) return true;
+  std::vector<cudaError_t> rc((size_t)W, cudaSuccess);
+  auto work = [&](int w) {
+    cudaSetDevice(s.device);
+    cudaError_t e = cudaStreamWaitEvent(s.st[w], s.start, 0);
+    size_t k = 0;
+    char *hp = static_cast<char *>(h), *dp = static_cast<char *>(d);
+    size_t prev_off = 0, prev_len = 0;
+    int prev_b = 0;
+    for (size_t c = (size_t)w; c < nchunks && e == cudaSuccess; c += (size_t)W, k++) {
+      const int b = (int)(k & 1);
+      const size_t off = c * kStageChunk, len = std::min(kStageChunk, bytes - off);
+      e = cudaEventSynchronize(s.ev[w][b]); // the buffer's previous transfer (this call or the last one) is over
+      if (e != cudaSuccess) break;
+      if (to_device) {
+        memcpy(s.buf[w][b], hp + off, len);
+        e = cudaMemcpyAsync(dp + off, s.buf[w][b], len, cudaMemcpyHostToDevice, s.st[w]);
+        if (e == cudaSuccess) e = cudaEventRecord(s.ev[w][b], s.st[w]);
+      } else {
+        e = cudaMemcpyAsync(s.buf[w][b], dp + off, len, cudaMemcpyDeviceToHost, s.st[w]);
+        if (e == cudaSuccess) e = cudaEventRecord(s.ev[w][b], s.st[w]);
+        if (k > 0 && e == cudaSuccess) { // the previous chunk has landed while this one is in flight
+          e = cudaEventSynchronize(s.ev[w][prev_b]);
+          memcpy(hp + prev_off, s.buf[w][prev_b], prev_len);
+        }
+        prev_off = off;
+        prev_len = len;
+        prev_b = b;
+      }
+    }
+    if (!to_device && k > 0 && e == cudaSuccess) {
+      e = cudaEventSynchronize(s.ev[w][prev_b]);
+      memcpy(hp + prev_off, s.buf[w][prev_b], prev_len);
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(s.done[w], s.st[w]);
+    rc[(size_t)w] = e;
+  };
+  std::vector<std::thread> th;
+  for (int w = 1; w < W; w++) th.emplace_back(work, w);
+  work(0);
+  for (auto &t : th) t.join();
+  *err = cudaSuccess;
+  for (int w = 0; w < W; w++) {
+    if (rc[(size_t)w] != cudaSuccess) *err = rc[(size_t)w];
+    else if (cudaStreamWaitEvent(ctx->stream, s.done[w], 0) != cudaSuccess) *err = cudaGetLastError();
+  }
+  return true;
+}
+} // namespace
+
+// Host <-> device copy on the context's stream; pageable host memory of kStageMin bytes or more is staged.
+cudaError_t copy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes) {
+  cudaError_t e = cudaSuccess;
+  if (bytes >= kStageMin && host_is_pageable(h_src) && staged_copy(ctx, d_dst, const_cast<void *>(h_src), bytes, true, &e)) return e;
+  return cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->stream);
+}
+cudaError_t copy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes) {
+  cudaError_t e = cudaSuccess;
+  if (bytes >= kStageMin && host_is_pageable(h_dst) && staged_copy(ctx, const_cast<void *>(d_src), h_dst, bytes, false, &e)) return e;
+  return cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+}
+
 } // namespace cgb
 
 using namespace cgb;
@@ -252,6 +389,13 @@ int cgb_ctx_sync(cgb_ctx *ctx) {
   return CGB_OK;
 }
 
+int cgb_ctx_set_progress(cgb_ctx *ctx, cgb_progress_fn fn, void *user) {
+  CGB_REQUIRE(ctx, "cgb_ctx_set_progress: ctx is NULL");
+  ctx->progress = fn;
+  ctx->progress_user = user;
+  return CGB_OK;
+}
+
 void *cgb_ctx_stream(cgb_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 int cgb_ctx_device(cgb_ctx *ctx) { return ctx ? ctx->device : -1; }
 int cgb_ctx_sm_count(cgb_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
@@ -279,7 +423,7 @@ int cgb_memcpy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes, i
   CGB_REQUIRE(ctx && (bytes == 0 || (d_dst && h_src)), "cgb_memcpy_h2d: NULL argument");
   if (bytes == 0) return CGB_OK;
   ScopedDevice sd(ctx->device);
-  CGB_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CGB_CUDA(copy_h2d(ctx, d_dst, h_src, bytes));
   if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));
   return CGB_OK;
 }
@@ -288,7 +432,7 @@ int cgb_memcpy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes, i
   CGB_REQUIRE(ctx && (bytes == 0 || (h_dst && d_src)), "cgb_memcpy_d2h: NULL argument");
   if (bytes == 0) return CGB_OK;
   ScopedDevice sd(ctx->device);
-  CGB_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CGB_CUDA(copy_d2h(ctx, h_dst, d_src, bytes));
   if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));
   return CGB_OK;
 }
@@ -305,7 +449,15 @@ int cgb_memcpy(cgb_ctx *ctx, void *dst, const void *src, size_t bytes, int sync)
   CGB_REQUIRE(ctx && (bytes == 0 || (dst && src)), "cgb_memcpy: NULL argument");
   if (bytes == 0) return CGB_OK;
   ScopedDevice sd(ctx->device);
-  CGB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
+  // direction from the pointers; a pageable host side goes through the staged path (the reference's std::vector
+  // uploads and downloads: src/LinearAlgebraTypes.hpp:109-119, src/CG.hpp:517-532)
+  cudaPointerAttributes as, ad;
+  const bool src_dev = cudaPointerGetAttributes(&as, src) == cudaSuccess && (as.type == cudaMemoryTypeDevice || as.type == cudaMemoryTypeManaged);
+  const bool dst_dev = cudaPointerGetAttributes(&ad, dst) == cudaSuccess && (ad.type == cudaMemoryTypeDevice || ad.type == cudaMemoryTypeManaged);
+  cudaGetLastError();
+  if (dst_dev && !src_dev) CGB_CUDA(copy_h2d(ctx, dst, src, bytes));
+  else if (src_dev && !dst_dev) CGB_CUDA(copy_d2h(ctx, dst, src, bytes));
+  else CGB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
   // pageable host memory may still be read after an async copy returns: callers that pass
   // borrowed std::vector storage rely on the wait the reference issues next (src/CG.hpp:169)
   if (sync) CGB_CUDA(cudaStreamSynchronize(ctx->stream));

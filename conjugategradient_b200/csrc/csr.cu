@@ -277,9 +277,9 @@ int cgb_csr_create(cgb_ctx *ctx, int64_t n, int64_t nnz, const double *h_vals, c
   cudaError_t e = cudaMalloc(&dv, sizeof(double) * (size_t)nnz + 64);
   if (e == cudaSuccess) e = cudaMalloc(&dc, sizeof(int32_t) * (size_t)nnz + 64);
   if (e == cudaSuccess) e = cudaMalloc(&dr, sizeof(int32_t) * (size_t)(n + 1) + 64);
-  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(dv, h_vals, sizeof(double) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream);
-  if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(dc, h_cols, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(dr, h_rowptr, sizeof(int32_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess && nnz) e = copy_h2d(ctx, dv, h_vals, sizeof(double) * (size_t)nnz);
+  if (e == cudaSuccess && nnz) e = copy_h2d(ctx, dc, h_cols, sizeof(int32_t) * (size_t)nnz);
+  if (e == cudaSuccess) e = copy_h2d(ctx, dr, h_rowptr, sizeof(int32_t) * (size_t)(n + 1));
   // the host arrays are only borrowed until this call returns (reference waits in setTarget, src/CG.hpp:169)
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) {
@@ -405,6 +405,9 @@ int cgb_gen_stencil(cgb_ctx *ctx, int kind, int64_t m, int64_t mz, int64_t row_b
   CGB_REQUIRE(n < ((int64_t)1 << 31), "cgb_gen_stencil: n must fit 32-bit column indices");
   ScopedDevice sd(ctx->device);
   const int64_t nloc = row_end - row_begin;
+  // row offsets are the reference's 32-bit ints (and the row lengths are scanned as such): bound the block's entries
+  CGB_REQUIRE(nloc * (kind == 2 ? 27 : kind == 1 ? 7 : 5) < ((int64_t)1 << 31),
+              "cgb_gen_stencil: this row block would hold 2^31 or more entries; generate it in smaller row ranges (one per GPU)");
   int32_t *rowptr = nullptr, *cols = nullptr;
   double *vals = nullptr;
   CGB_CUDA(cudaMalloc(&rowptr, sizeof(int32_t) * (size_t)(nloc + 1) + 64));

@@ -544,6 +544,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     launches += (int64_t)batch * per_iter;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaStreamSynchronize(s));
+    if (ctx->progress) ctx->progress((int64_t)w.h_st[0].iter, n_global, w.h_st[0].rr, ctx->progress_user);
     if (w.h_st[0].done || w.h_st[0].iter >= w.h_st[0].max_iter || w.h_st[0].comm_error) break;
   }
   if (w.h_st[0].comm_error) {

@@ -377,6 +377,7 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   if (occ < 1) return fail(CGB_ERR_CUDA, "cg_dist_persistent_kernel: does not fit an SM");
   int grid = std::min(occ * d->ctx->sm_count, kMaxPartials);
   if (const char *e = getenv("CGB_DIST_PERSISTENT_CTAS")) grid = std::max(1, std::min(grid, atoi(e)));
+  if (!d->bar) CGB_CUDA(cudaMalloc(&d->bar, sizeof(DistBar)));
   DistLoopArgs a;
   memset(&a, 0, sizeof(a));
   a.A = csr_view(A);
@@ -403,7 +404,6 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   a.bar = static_cast<DistBar *>(d->bar);
   a.timeout_cycles = timeout_cycles;
   if (const char *e = getenv("CGB_DIST_JITTER_NS")) a.jitter_ns = (unsigned)std::max(0, atoi(e));
-  if (!d->bar) CGB_CUDA(cudaMalloc(&d->bar, sizeof(DistBar)));
   CGB_CUDA(cudaMemsetAsync(d->bar, 0, sizeof(DistBar), s));
   void *args[] = {&a};
   CGB_CUDA(cudaLaunchCooperativeKernel((void *)kernel, dim3(grid), dim3(kTmaThreads), args, smem, s));

@@ -91,12 +91,21 @@ public:
       x.init_empty(N);
     }
     log("Prepared Memory");
+    if constexpr (debug == Debuglevel::Verbose) { // the reference's percentage line (:428-433), driven by the per-batch poll
+      _progress_mark = -1;
+      cgb_ctx_set_progress(_queue.native(), &CG::progress, this);
+    }
     try {
       asycl::detail::check(
           cgb_cg_solve(_queue.native(), A.csr(), b.ptr(), x.ptr(), improvement, /*max_iter = N + 1*/ -1, &_opts, &_stats));
     } catch (std::exception &e) {
+      if constexpr (debug == Debuglevel::Verbose) cgb_ctx_set_progress(_queue.native(), nullptr, nullptr);
       std::cerr << "Caught Exception " << e.what() << std::endl;
       throw;
+    }
+    if constexpr (debug == Debuglevel::Verbose) {
+      cgb_ctx_set_progress(_queue.native(), nullptr, nullptr);
+      if (_progress_mark >= 0) std::clog << "\r\033[2K";
     }
     this->is_solved = true;
     if constexpr (debug == Debuglevel::Verbose) {
@@ -139,6 +148,17 @@ private:
   void log(const char *what) {
     if constexpr (debug == Debuglevel::Verbose) std::clog << what << "\n";
   }
+  // Same text as the reference: the trip counter as a percentage of N, refreshed every 100 trips (:428-433).  The
+  // device-side loop is polled once per batch, so the line moves at the first poll past each multiple of 100.
+  static void progress(int64_t trips, int64_t n, double /*rr*/, void *self) {
+    CG *me = static_cast<CG *>(self);
+    const long long mark = (long long)(trips / 100);
+    if (mark == me->_progress_mark || n <= 0) return;
+    me->_progress_mark = mark;
+    std::clog << "\r\033[2K";
+    std::clog << ((static_cast<double>(trips) / static_cast<double>(n)) * 100) << "%";
+    std::flush(std::clog);
+  }
   void executeQueue() {
     try {
       this->_queue.wait_and_throw();
@@ -155,6 +175,7 @@ private:
   Vector b;
   cgb_cg_opts _opts;
   cgb_cg_stats _stats;
+  long long _progress_mark = -1;
 };
 
 } // namespace CGSolver

@@ -56,6 +56,13 @@ void *cgb_ctx_stream(cgb_ctx *ctx);
 int cgb_ctx_device(cgb_ctx *ctx);
 int cgb_ctx_sm_count(cgb_ctx *ctx);
 
+/* Progress of a running solve, for the reference's Debuglevel::Verbose percentage line (src/CG.hpp:428-433: it
+ * prints counter / N every 100 trips).  The callback runs on the calling host thread each time the solve polls the
+ * device-side state (once per batch of check_every trips); the one-kernel loops for small systems never poll.
+ * fn == NULL removes it. */
+typedef void (*cgb_progress_fn)(int64_t trips, int64_t n, double rr, void *user);
+int cgb_ctx_set_progress(cgb_ctx *ctx, cgb_progress_fn fn, void *user);
+
 /* ---- raw device memory ---------------------------------------------------------------------
  * replaces: asycl::malloc_device / free / queue.copy / queue.fill
  * (src/LinearAlgebraTypes.hpp:43-49,109-119,160-183,213-224).  Allocations are 256-byte aligned.
@@ -221,7 +228,8 @@ typedef struct cgb_cg_stats {
 void cgb_cg_default_opts(cgb_cg_opts *opts);
 /* Device-resident solve.  d_x: in = initial guess, out = solution (CG::setInital / x zeros,
  * src/CG.hpp:215-219,291-297).  max_iter < 0 means the reference cap n+1.  Work vectors are
- * cached inside the csr handle and reused across solves. */
+ * cached inside the csr handle and reused across solves.  d_x must be 16-byte aligned (every cgb_malloc'ed
+ * pointer is; an odd-offset sub-vector is refused with CGB_ERR_INVALID): the update kernels use 128-bit accesses. */
 int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,
                  const cgb_cg_opts *opts, cgb_cg_stats *stats);
 /* Host-buffer solve: what Tester.cpp does between setMatrix and extract (test/Tester.cpp:36-49):

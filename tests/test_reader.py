@@ -106,3 +106,17 @@ def test_reader_vs_reference_speed(tmp_path, ref_serial, capsys):
     with capsys.disabled():
         print(f"\n[reader] n={r.size - 1} nnz={v.size}: reference read_file {t_ref:.3f} s, cgb_mm_read {t_ours:.3f} s")
     assert t_ours < t_ref
+
+
+@pytest.mark.gpu
+def test_empty_row_is_refused(tmp_path):
+    """The reference dialect compacts empty rows away without renumbering columns (test/mm_reader.cpp:92-104): its
+    spmv then reads outside the vector.  The device path refuses such a file instead of faulting."""
+    from conjugategradient_b200 import _lib as L
+    from conjugategradient_b200 import solver as S
+    p = tmp_path / "hole.mtx"
+    p.write_text("%%MatrixMarket matrix coordinate real symmetric\n% row 3 is empty\n4 4 4\n1 1 2.0\n2 2 2.0\n2 1 -1.0\n4 4 2.0\n")
+    ctx = S.Context(0)
+    with pytest.raises(L.CgbError) as e:
+        S.Matrix.from_mm_file(ctx, str(p))
+    assert e.value.code == L.CGB_ERR_INVALID and "empty row" in str(e.value)

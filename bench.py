@@ -141,6 +141,35 @@ def ncu_traffic(workload):
     return None, None
 
 
+_GATHER_PEAK = {}
+
+
+def l2_roofline(nnz, k1_ms, rig):
+    """The SELL engine on a random matrix is bound by the L2 -> SM path, not by HBM: every gathered double pulls a
+    32-byte sector out of the L2-resident column panel of p.  Peak = tools/gather_bench.cu run live (random 8-byte
+    gathers from a 40 MB vector, nothing else); achieved = (32 B per gather + the 12 B per entry of the matrix stream,
+    which crosses the same path) / the kernel's time."""
+    exe = os.path.join(ROOT, "tools", "_build", "gather_bench")
+    if "v" not in _GATHER_PEAK:
+        _GATHER_PEAK["v"] = None
+        if os.path.exists(exe) and rig.world == 1:
+            try:
+                env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(rig.local_rank))
+                out = subprocess.run([exe, "40", str(1 << 27), "3"], capture_output=True, text=True, timeout=120, env=env)
+                _GATHER_PEAK["v"] = json.loads(out.stdout.strip().splitlines()[-1])
+            except Exception:  # noqa: BLE001
+                _GATHER_PEAK["v"] = None
+    g = _GATHER_PEAK["v"]
+    if not g:
+        return None
+    by = 32 * nnz + 12 * nnz
+    ach = by / (k1_ms * 1e6)
+    return {"bound": "l2_to_sm", "bytes_per_launch": by, "achieved": ach, "unit": "GB/s",
+            "peak": g["l2_to_sm_sector_GBps"], "frac": ach / g["l2_to_sm_sector_GBps"],
+            "gathers_per_s_kernel": nnz / (k1_ms * 1e-3), "gathers_per_s_peak": g["gathers_per_s"],
+            "peak_source": "tools/gather_bench.cu, live: random 8-byte gathers out of a 40 MB vector, 32 B sector per gather"}
+
+
 def golden_parity(workload):
     if os.path.exists(GOLDEN_PARITY):
         return json.load(open(GOLDEN_PARITY)).get(workload)
@@ -489,6 +518,7 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
                     "frac_of_8TBps_spec": ach / 8000.0,
                     "iteration_GBps_B_iter": it_gbps, "iteration_frac_of_peak": it_gbps / peak,
                     "iteration_frac_of_8TBps": it_gbps / 8000.0,
+                    "l2": l2_roofline(nnz, k1_ms, rig) if last["format"] == L.FMT_SELL else None,
                     "note": "frac can exceed 1: the peak is a COPY (half reads, half writes); this kernel's traffic is 93 % reads, "
                             "which HBM3e serves faster than a 50/50 mix. The spec-based fraction is frac_of_8TBps_spec."}
 
@@ -640,6 +670,21 @@ def run_ours(args):
                      "achieved_GBps_B_iter": r["achieved_GBps_B_iter"], "roofline": r["roofline"], "e2e": r["e2e"],
                      "cpu_baseline": r["cpu_baseline"], "parity": r["parity"], "run": r["run"], "wall_s": round(time.time() - t0, 1)}
             others[BASELINE_NAME[wl]] = entry
+    # ---- the drop-in C++ headers end to end from pageable std::vector storage (C2) ----------
+    e2e_cpp = None
+    exe = os.path.join(ROOT, "examples", "e2e_cpp")
+    if world == 1 and not args.no_e2e and args.configs != "none" and os.path.exists(exe):
+        try:
+            out = subprocess.run([exe, "128", "3", "1"], capture_output=True, text=True, timeout=300)
+            e2e_cpp = json.loads(out.stdout.strip().splitlines()[-1])
+            e2e_cpp["api"] = ("include/CG.hpp: createCG + setMatrix(std::vector) + setTarget + solve + extract per step, pageable host "
+                              "memory (examples/e2e_cpp.cpp; reference protocol test/Tester.cpp:36-49), wall clock")
+            e2e_cpp["config"] = "C2 (3D 7-pt 128^3)"
+            pinned = (others.get("C2") or {}).get("e2e") or {}
+            if pinned.get("value"):
+                e2e_cpp["vs_pinned_c_abi_e2e"] = e2e_cpp["value"] / pinned["value"]
+        except Exception as e:  # noqa: BLE001
+            e2e_cpp = {"unavailable": f"{type(e).__name__}: {e}"}
     if rank == 0:
         line = {
             "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -649,7 +694,7 @@ def run_ours(args):
             "run": head["run"], "roofline": head["roofline"], "cpu_baseline": head["cpu_baseline"], "e2e": head["e2e"],
             "parity": head["parity"], "gpu_launches": head["launches"], "clocks": head["clocks"],
             "achieved_GBps_B_iter": head["achieved_GBps_B_iter"], "opt_in_format": head["opt_in_format"],
-            "configs": others,
+            "configs": others, "e2e_cpp": e2e_cpp,
         }
         emit(line)
     rig.close()

@@ -87,21 +87,38 @@ __device__ __forceinline__ void st_release_gpu_u64(unsigned long long *p, unsign
 }
 
 // Spin until *flag >= want (SYS = flag written by a peer GPU).  False on time-out or when another CTA reported one.
+// The poll is a RELAXED load and the acquire is one fence after it succeeds: an acquire load per poll would
+// invalidate the SM's L1 on every spin (CCTL.IVALL), under the feet of the co-resident CTAs that are still gathering.
+template <bool SYS>
+__device__ __forceinline__ unsigned long long dist_poll(const unsigned long long *p) {
+  unsigned long long v;
+  if (SYS) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  else asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+template <bool SYS>
+__device__ __forceinline__ void dist_acquire_fence() {
+  if (SYS) asm volatile("fence.acq_rel.sys;" ::: "memory");
+  else asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
 template <bool SYS>
 __device__ __forceinline__ bool dist_wait(const unsigned long long *flag, unsigned long long want, CgState *st, long long limit) {
-  if ((SYS ? ld_acquire_sys_u64(flag) : ld_acquire_gpu_u64(flag)) >= want) return true;
-  const long long t0 = clock64();
-  int spins = 0;
-  while ((SYS ? ld_acquire_sys_u64(flag) : ld_acquire_gpu_u64(flag)) < want) {
-    if ((++spins & 63) == 0) {
-      if (*(volatile int *)&st->comm_error) return false;
-      if (clock64() - t0 > limit) {
-        *(volatile int *)&st->comm_error = 1;
-        __threadfence();
-        return false;
+  if (dist_poll<SYS>(flag) < want) {
+    const long long t0 = clock64();
+    int spins = 0;
+    while (dist_poll<SYS>(flag) < want) {
+      __nanosleep(20);
+      if ((++spins & 63) == 0) {
+        if (*(volatile int *)&st->comm_error) return false;
+        if (clock64() - t0 > limit) {
+          *(volatile int *)&st->comm_error = 1;
+          __threadfence();
+          return false;
+        }
       }
     }
   }
+  dist_acquire_fence<SYS>();
   return true;
 }
 
@@ -168,13 +185,35 @@ __device__ __forceinline__ double dist_allreduce(double v, const DistLoopArgs &a
   return sum;
 }
 
+// The vector phases run on the SpMV's launch shape (3 CTAs of 288 threads per SM, less than half the threads the
+// stand-alone vector kernels use): every thread keeps UNROLL independent 16-byte loads per array in flight instead.
 __device__ __forceinline__ void dist_pupdate_body(int64_t n, const double *r, double *p, double *x, double alpha, double beta) {
+  constexpr int UNROLL = 2;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   const int64_t n2 = n >> 1;
   const double2 *r2 = reinterpret_cast<const double2 *>(r);
   double2 *p2 = reinterpret_cast<double2 *>(p);
   double2 *x2 = reinterpret_cast<double2 *>(x);
-  for (int64_t i = tid; i < n2; i += nthr) {
+  int64_t i = tid;
+  for (; i + (UNROLL - 1) * nthr < n2; i += UNROLL * nthr) {
+    double2 rv[UNROLL], pv[UNROLL], xv[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; u++) {
+      rv[u] = r2[i + u * nthr];
+      pv[u] = p2[i + u * nthr];
+      xv[u] = x2[i + u * nthr];
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; u++) {
+      xv[u].x = fma(alpha, pv[u].x, xv[u].x);
+      xv[u].y = fma(alpha, pv[u].y, xv[u].y);
+      pv[u].x = fma(beta, pv[u].x, rv[u].x);
+      pv[u].y = fma(beta, pv[u].y, rv[u].y);
+      x2[i + u * nthr] = xv[u];
+      p2[i + u * nthr] = pv[u];
+    }
+  }
+  for (; i < n2; i += nthr) {
     const double2 rv = r2[i];
     double2 pv = p2[i];
     double2 xv = x2[i];
@@ -206,12 +245,31 @@ __device__ __forceinline__ void dist_jitter(const DistLoopArgs &a, unsigned salt
 // r -= alpha Ap, this thread's share of r.r.  No __restrict__ / const here: Ap is written by other CTAs of this very kernel,
 // so its loads must stay on the coherent path (cg_update_body's qualifiers would allow ld.global.nc).
 __device__ __forceinline__ double dist_update_body(int64_t n, double *r, double *Ap, double alpha) {
+  constexpr int UNROLL = 4;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   const int64_t n2 = n >> 1;
   double2 *r2 = reinterpret_cast<double2 *>(r);
   double2 *q2 = reinterpret_cast<double2 *>(Ap);
   double acc = 0.0;
-  for (int64_t i = tid; i < n2; i += nthr) {
+  int64_t i = tid;
+  // the order in which a thread adds its squares is fixed by (n, grid): results stay bitwise reproducible
+  for (; i + (UNROLL - 1) * nthr < n2; i += UNROLL * nthr) {
+    double2 rv[UNROLL], qv[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; u++) {
+      rv[u] = r2[i + u * nthr];
+      qv[u] = q2[i + u * nthr];
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; u++) {
+      rv[u].x = fma(-alpha, qv[u].x, rv[u].x);
+      rv[u].y = fma(-alpha, qv[u].y, rv[u].y);
+      r2[i + u * nthr] = rv[u];
+      acc = fma(rv[u].x, rv[u].x, acc);
+      acc = fma(rv[u].y, rv[u].y, acc);
+    }
+  }
+  for (; i < n2; i += nthr) {
     double2 rv = r2[i];
     const double2 qv = q2[i];
     rv.x = fma(-alpha, qv.x, rv.x);

@@ -640,7 +640,9 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
                     else "one persistent cooperative kernel per solve (grid-wide barriers)" if last["loop_mode"] == L.LOOP_PERSISTENT
                     else "CUDA graph batches of %d iterations, device-side stop flag, polled one batch behind" % args.check_every),
            "engine": {L.FMT_SELL: "SELL-32-sigma", L.FMT_DICT: "row-pattern dictionary (explicit option)"}.get(last["format"], "CSR TMA-staged"),
-           "transport": (os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None)}
+           "transport": (os.environ.get("CGB_DIST_TRANSPORT", "peer") if world > 1 else None),
+           "exchange": (None if world == 1 else "all-gather of p over NVLink (dense coupling)" if lib.cgb_dist_exchange_mode(rig.dh) == 1
+                        else "halo entries only")}
     return {"kind": kind, "m": m, "rel": rel, "n": n, "nnz": nnz, "value": value, "ms_total": ms_total, "steps": steps,
             "warmup": warmup, "iters": iters, "launches": int(launches), "clocks": clocks, "roofline": roof, "e2e": e2e,
             "cpu_baseline": cpu, "parity": parity, "run": run, "opt_in_format": extra_fmt,

@@ -122,6 +122,7 @@ SIGNATURES = {
     "cgb_dist_cg_solve": (C.c_int, [c_vp, c_vp, c_vp, C.c_double, c_i64, C.POINTER(CgOpts), C.POINTER(CgStats)]),
     "cgb_dist_residual": (C.c_int, [c_vp, c_vp, c_vp, c_dp, c_dp]),
     "cgb_dist_halo_count": (c_i64, [c_vp]),
+    "cgb_dist_exchange_mode": (C.c_int, [c_vp]),
     "cgb_plan_halo": (C.c_int, [C.c_int, C.c_int, c_vp, c_i64, c_vp, c_vp, c_i64, C.POINTER(c_i64), c_vp]),
 }
 

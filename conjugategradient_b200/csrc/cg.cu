@@ -25,6 +25,7 @@ static cudaAccessPolicyWindow p_window(cgb_ctx *ctx, const double *p, int64_t n)
   w.num_bytes = bytes;
   const double ratio = bytes ? (double)ctx->l2_persist_set / (double)bytes : 0.0;
   w.hitRatio = (float)(ratio > 1.0 ? 1.0 : ratio);
+  if (const char *e = getenv("CGB_L2_HITRATIO")) w.hitRatio = (float)std::min(1.0, std::max(0.0, atof(e))); // A/B runs (profiles/r02_l2window.md)
   w.hitProp = cudaAccessPropertyPersisting;
   w.missProp = cudaAccessPropertyStreaming;
   return w;
@@ -60,10 +61,10 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
     constexpr int T = decltype(Tc)::value;
     if (c.fused)
       launch_kernel(cg_spmv_kernel<L, T, true>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, x, w.st, w.partials,
-                    (double *)nullptr);
+                    (double *)nullptr, (const double *)nullptr);
     else
       launch_kernel(cg_spmv_kernel<L, T, false>, c.sl, s, V, (const double *)w.r, w.p0, w.p1, w.Ap, x, w.st, w.partials,
-                    (double *)nullptr);
+                    (double *)nullptr, (const double *)nullptr);
   });
   CGB_CUDA(mark(2));
   if (c.jacobi) cg_update_jacobi_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.dinv, w.st, w.partials, w.hist);
@@ -115,10 +116,17 @@ static int build_graph(cgb_csr *A, double *x, const LoopCfg &c, int batch, uint6
     cudaKernelNodeAttrValue v;
     memset(&v, 0, sizeof(v));
     v.accessPolicyWindow = p_window(A->ctx, w.p0, A->n);
+    // CGB_L2_WINDOW_MODE=k1: only the SpMV nodes (the gathers) carry the window; default: every kernel of the trip
+    const char *wm = getenv("CGB_L2_WINDOW_MODE");
+    const bool k1_only = wm && !strcmp(wm, "k1");
     for (size_t i = 0; i < nn; i++) {
       cudaGraphNodeType t;
-      if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel)
-        cudaGraphKernelNodeSetAttribute(nodes[i], cudaKernelNodeAttributeAccessPolicyWindow, &v);
+      if (cudaGraphNodeGetType(nodes[i], &t) != cudaSuccess || t != cudaGraphNodeTypeKernel) continue;
+      if (k1_only) {
+        cudaKernelNodeParams kp;
+        if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess || kp.blockDim.x != (unsigned)c.sl.block || kp.gridDim.x != (unsigned)c.sl.grid) continue;
+      }
+      cudaGraphKernelNodeSetAttribute(nodes[i], cudaKernelNodeAttributeAccessPolicyWindow, &v);
     }
     cudaGetLastError();
   }
@@ -262,7 +270,10 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (const char *e = getenv("CGB_L2_WINDOW")) l2w = atoi(e) != 0;
   l2w = l2w && !fused && ctx->l2_persist_max > 0 && ctx->l2_window_max > 0;
   if (l2w && ctx->l2_persist_set == 0) {
-    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_persist_max) == cudaSuccess) ctx->l2_persist_set = ctx->l2_persist_max;
+    // carve-out: the device maximum, or CGB_L2_CARVE_MB (A/B runs: a carve-out sized to the window instead)
+    size_t carve = ctx->l2_persist_max;
+    if (const char *e = getenv("CGB_L2_CARVE_MB")) carve = std::min(carve, (size_t)(atof(e) * 1048576.0));
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess) ctx->l2_persist_set = carve;
     else {
       cudaGetLastError();
       l2w = false;
@@ -286,7 +297,8 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
     }
   }
   LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, jacobi, replace, d_b};
-  if (l2w) {
+  const char *l2mode = getenv("CGB_L2_WINDOW_MODE");
+  if (l2w && !(l2mode && !strcmp(l2mode, "k1"))) { // (k1: the window rides on the SpMV graph nodes only)
     cudaStreamAttrValue v;
     memset(&v, 0, sizeof(v));
     v.accessPolicyWindow = p_window(ctx, w.p0, n);

@@ -163,7 +163,10 @@ static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, co
 template <int L, int ENG, bool FUSED>
 __global__ void CGB_BOUNDS(ENG) cg_spmv_kernel(CsrView A, const double *__restrict__ r, double *pbuf0,
                                                           double *pbuf1, double *__restrict__ Ap, double *x,
-                                                          CgState *st, double *partials, double *local_out) {
+                                                          CgState *st, double *partials, double *local_out,
+                                                          const double *gather) {
+  // gather != NULL (multi-GPU all-gather mode, unfused only): the matrix has GLOBAL columns and gathers from the
+  // all-gathered copy of p, while pbuf0 stays this rank's own slice (the p[i] of the p.Ap epilogue)
   if (!cg_active(st)) return;
   __shared__ double red[32];
   double a0 = 0.0, a1 = 0.0;
@@ -176,7 +179,7 @@ __global__ void CGB_BOUNDS(ENG) cg_spmv_kernel(CsrView A, const double *__restri
     EpiDotFusedP e{Ap, r, p_old, p_new, x, beta, st->alpha};
     spmv_rows<L, ENG>(A, g, e, a0, a1);
   } else {
-    GatherPlain g{pbuf0};
+    GatherPlain g{gather ? gather : pbuf0};
     EpiDotP e{Ap, pbuf0};
     spmv_rows<L, ENG>(A, g, e, a0, a1);
   }

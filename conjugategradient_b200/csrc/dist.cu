@@ -86,6 +86,9 @@ struct PeerSend { // where the entries of the packed send list go: slice q -> ds
 struct PeerRecv {
   int from[kMaxRanks]; // 1 where this rank receives halo entries from that rank
 };
+struct PeerGather { // all-gather mode: where this rank's slice goes in every rank's full-length copy (dst[rank] = local copy)
+  double *dst[kMaxRanks];
+};
 } // namespace cgb
 
 struct cgb_dist {
@@ -117,6 +120,13 @@ struct cgb_dist {
   std::vector<double *> halo_of;        // peers' halo buffers as mapped here (nullptr where nothing is sent)
   PeerSend send;                        // destination table of the pack kernel
   PeerRecv recv;                        // which ranks this rank receives from
+  // all-gather mode (dense coupling: most remote entries are needed): the block keeps its GLOBAL columns and
+  // gathers from a full-length copy of the vector that every rank fills with its slice over NVLink
+  bool allgather = false;
+  double *pfull = nullptr;              // n_global doubles (IPC-exported)
+  size_t pfull_bytes = 0;
+  std::vector<double *> pfull_of;       // peers' copies as mapped here
+  PeerGather gather;
   void *bar = nullptr;                  // DistBar of the persistent loop (dist_persistent.cuh)
   bool dead = false;                    // a peer wait timed out: windows and sequence numbers are inconsistent across ranks
   PeerCtx pctx() const { return PeerCtx{rank, nranks, d_win, seq}; }
@@ -536,6 +546,41 @@ __global__ void __launch_bounds__(kBlock) peer_resid_kernel(int64_t n, const dou
   }
 }
 
+// All-gather mode: this rank's slice of `vec` goes into every rank's full-length copy (coalesced 16-byte NVLink stores),
+// the last CTA raises this rank's flag in every window.
+__global__ void __launch_bounds__(kBlock) peer_allgather_kernel(int64_t n, const double *__restrict__ vec, PeerGather pg,
+                                                                 PeerCtx pc, CgState *st, int gated) {
+  if (gated && !cg_active(st)) return;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n2 = n >> 1;
+  const double2 *v2 = reinterpret_cast<const double2 *>(vec);
+  for (int64_t i = tid; i < n2; i += nthr) {
+    const double2 v = v2[i];
+    for (int q = 0; q < pc.nranks; q++) reinterpret_cast<double2 *>(pg.dst[q])[i] = v;
+  }
+  if ((n & 1) && tid == 0)
+    for (int q = 0; q < pc.nranks; q++) pg.dst[q][n - 1] = vec[n - 1];
+  __threadfence_system();
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const unsigned long long s = pc.seq->halo + 1;
+    const int q = threadIdx.x;
+    if (q < pc.nranks && q != pc.rank) {
+      __threadfence_system();
+      st_release_sys_u64(&pc.win[q]->hflag[pc.rank], s);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) pc.seq->halo = s;
+  }
+}
+
+// All-gather mode: one warp waits until every peer's slice has arrived; the SpMV launches behind it in the stream.
+__global__ void peer_flags_wait_kernel(PeerCtx pc, PeerRecv pr, CgState *st, int gated) {
+  if (gated && !cg_active(st)) return;
+  bool ok = true;
+  if (threadIdx.x < pc.nranks && pr.from[threadIdx.x]) ok = peer_wait(&pc.win[pc.rank]->hflag[threadIdx.x], pc.seq->halo);
+  if (!ok) peer_fail(st);
+}
+
 template <class T>
 int d2h_vec(cgb_ctx *ctx, std::vector<T> &out, const T *d, size_t n) {
   out.resize(n);
@@ -552,6 +597,13 @@ int owner_of(const std::vector<int64_t> &rs, int64_t col) {
 // On return the comm stream has ev_halo recorded; the caller makes the main stream wait for it.
 int halo_exchange(cgb_dist *d, const double *vec, int gated) {
   cudaStream_t s = d->ctx->stream, c = d->comm_stream;
+  if (d->allgather) { // the whole slice to every rank, then wait for everybody else's
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->n / 2 + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 4));
+    peer_allgather_kernel<<<grid, kBlock, 0, s>>>(d->n, vec, d->gather, d->pctx(), d->Aloc->ws.st, gated);
+    peer_flags_wait_kernel<<<1, 32, 0, s>>>(d->pctx(), d->recv, d->Aloc->ws.st, gated);
+    CGB_CUDA(cudaGetLastError());
+    return CGB_OK;
+  }
   if (d->peer) {
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->S + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 2));
     peer_pack_kernel<<<grid, kBlock, 0, s>>>(d->S, d->send_idx, vec, d->send, d->pctx(), d->Aloc->ws.st, gated);
@@ -581,6 +633,13 @@ int peer_halo_apply(cgb_dist *d, double *y, const double *p, const double *base,
   Workspace &w = d->Aloc->ws;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((d->nh + kBlock - 1) / kBlock, (int64_t)d->ctx->sm_count * 4));
   cgb_csr *H = d->Ahalo;
+  if (!H) { // all-gather mode: no halo part; mode 1 still all-reduces p.Ap and forms alpha
+    if (mode == 1)
+      peer_halo_kernel<1><<<1, kBlock, 0, s>>>(0, nullptr, nullptr, nullptr, nullptr, nullptr, y, p, base, d->pctx(), d->recv, w.st,
+                                               gated, w.partials);
+    CGB_CUDA(cudaGetLastError());
+    return CGB_OK;
+  }
   int64_t engine_min = kHaloEngineMinNnz;
   if (const char *e = getenv("CGB_HALO_ENGINE_MIN")) engine_min = atoll(e);
   if (H->nnz >= engine_min && H->n > 0) { // a real share of the matrix: regular row engines over A_halo
@@ -674,6 +733,9 @@ static void peer_release_halo(cgb_dist *d) {
   for (size_t q = 0; q < d->halo_of.size(); q++)
     if ((int)q != d->rank && d->halo_of[q]) cudaIpcCloseMemHandle(d->halo_of[q]);
   d->halo_of.clear();
+  for (size_t q = 0; q < d->pfull_of.size(); q++)
+    if ((int)q != d->rank && d->pfull_of[q]) cudaIpcCloseMemHandle(d->pfull_of[q]);
+  d->pfull_of.clear();
   if (d->peer && d->comm && d->scal) { // barrier
     g_nccl.AllReduce(d->scal + 6, d->scal + 7, 1, ncclDouble, ncclSum, d->comm, d->ctx->stream);
     cudaStreamSynchronize(d->ctx->stream);
@@ -690,6 +752,9 @@ static void dist_release_matrix(cgb_dist *d) {
   cudaFree(d->send_idx);
   cudaFree(d->send_buf);
   cudaFree(d->halo);
+  cudaFree(d->pfull);
+  d->pfull = nullptr;
+  d->allgather = false;
   d->Aloc = d->Ahalo = nullptr;
   d->halo_rows = nullptr;
   d->send_idx = nullptr;
@@ -722,6 +787,7 @@ int cgb_dist_destroy(cgb_dist *d) {
 }
 
 int64_t cgb_dist_halo_count(const cgb_dist *d) { return d ? d->H : 0; }
+int cgb_dist_exchange_mode(const cgb_dist *d) { return d && d->allgather ? 1 : 0; }
 
 } // extern "C"
 

@@ -167,6 +167,72 @@ int peer_halo_setup(cgb_dist *d, const std::vector<int64_t> &M) {
   return CGB_OK;
 }
 
+// All-gather mode set-up: A_loc = a copy of the caller's block as it is (global columns), no halo part; a full-length
+// buffer for the gathered vector, exported to the peers, and the peers' buffers mapped here.
+int dist_setup_allgather(cgb_dist *d, cgb_csr *A, PhaseTimer &pt) {
+  cgb_ctx *ctx = d->ctx;
+  cudaStream_t s = ctx->stream;
+  const int P = d->nranks;
+  const int64_t n = A->n, n_global = d->row_starts[P], lo = d->row_starts[d->rank];
+  DevBuf g_r, g_c, g_v;
+  CGB_TRY(dev_alloc(g_r, sizeof(int32_t) * (size_t)(n + 1) + 64));
+  CGB_TRY(dev_alloc(g_c, sizeof(int32_t) * (size_t)A->nnz + 64));
+  CGB_TRY(dev_alloc(g_v, sizeof(double) * (size_t)A->nnz + 64));
+  CGB_CUDA(cudaMemcpyAsync(g_r.p, A->rowptr, sizeof(int32_t) * (size_t)(n + 1), cudaMemcpyDeviceToDevice, s));
+  CGB_CUDA(cudaMemcpyAsync(g_c.p, A->cols, sizeof(int32_t) * (size_t)A->nnz, cudaMemcpyDeviceToDevice, s));
+  CGB_CUDA(cudaMemcpyAsync(g_v.p, A->vals, sizeof(double) * (size_t)A->nnz, cudaMemcpyDeviceToDevice, s));
+  CGB_TRY(cgb_csr_from_device(ctx, n, A->nnz, g_v.as<double>(), g_c.as<int32_t>(), g_r.as<int32_t>(), 1, &d->Aloc));
+  g_r.p = g_c.p = g_v.p = nullptr;
+  d->Aloc->n_cols = n_global; // the gathered vector is the full-length copy: column panels are sized from it
+  if (A->format != CGB_FMT_AUTO) {
+    const int rc = cgb_csr_set_format(d->Aloc, A->format);
+    if (rc != CGB_OK && rc != CGB_ERR_UNSUPPORTED) return rc;
+  }
+  d->Ahalo = nullptr;
+  d->nh = 0;
+  d->S = 0;
+  d->rcount.assign(P, 0);
+  d->scount.assign(P, 0);
+  d->roff.assign(P + 1, 0);
+  d->soff.assign(P + 1, 0);
+  memset(&d->send, 0, sizeof(d->send));
+  memset(&d->recv, 0, sizeof(d->recv));
+  for (int q = 0; q < P; q++) d->recv.from[q] = q != d->rank && d->row_starts[q + 1] > d->row_starts[q];
+  d->pfull_bytes = ((sizeof(double) * (size_t)(n_global + 2) + kIpcGranule - 1) / kIpcGranule) * kIpcGranule;
+  CGB_CUDA(cudaMalloc(&d->pfull, d->pfull_bytes));
+  CGB_CUDA(cudaMemsetAsync(d->pfull, 0, d->pfull_bytes, s));
+  CGB_CUDA(cudaStreamSynchronize(s));
+  pt.mark("setup: all-gather block copy");
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  int ok = cudaIpcGetMemHandle(&mine, d->pfull) == cudaSuccess;
+  if (!ok) cudaGetLastError();
+  std::vector<cudaIpcMemHandle_t> all;
+  CGB_TRY(gather_ipc_handles(d, mine, all));
+  d->pfull_of.assign(P, nullptr);
+  memset(&d->gather, 0, sizeof(d->gather));
+  for (int q = 0; q < P; q++) {
+    if (q == d->rank) {
+      d->pfull_of[q] = d->pfull;
+    } else if (ok) {
+      void *ptr = nullptr;
+      if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+      } else {
+        d->pfull_of[q] = (double *)ptr;
+      }
+    }
+    if (d->pfull_of[q]) d->gather.dst[q] = d->pfull_of[q] + lo;
+  }
+  int everyone = 0;
+  CGB_TRY(all_agree(d, ok, &everyone));
+  if (!everyone) return fail(CGB_ERR_NCCL, "all-gather mode: mapping a peer's vector buffer failed (set CGB_DIST_ALLGATHER=0)");
+  d->allgather = true;
+  pt.mark("setup: all-gather mapping");
+  return CGB_OK;
+}
+
 int dist_setup(cgb_dist *d, cgb_csr *A) {
   cgb_ctx *ctx = d->ctx;
   cudaStream_t s = ctx->stream;
@@ -259,6 +325,17 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   d->H = H;
 
   pt.mark("setup: receive list");
+  // Dense coupling (a random matrix: nearly every remote entry of the vector is needed by every rank): keep the block
+  // whole with its global columns and all-gather the vector instead of splitting off a halo part that would be most
+  // of the matrix ("if the union of needed remote columns is >~ half of n, all-gather p").
+  {
+    const int64_t n_global = d->row_starts[d->nranks];
+    int want = d->peer && n_global - n > 0 && (double)H >= 0.5 * (double)(n_global - n) && nnz_halo * 2 > (int64_t)A->nnz / 2;
+    if (const char *e = getenv("CGB_DIST_ALLGATHER")) want = d->peer && atoi(e) != 0;
+    int all = 0;
+    CGB_TRY(all_agree(d, want, &all));
+    if (all) return dist_setup_allgather(d, A, pt);
+  }
   // fill both parts
   int32_t *cols_loc = nullptr, *cols_halo = nullptr;
   double *vals_loc = nullptr, *vals_halo = nullptr;
@@ -349,10 +426,20 @@ int dist_enqueue_iteration(cgb_dist *d, double *x) {
   const SpmvLaunch lc = spmv_launch_cfg(A);
   cg_pupdate_kernel<<<A->grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_TRY(halo_exchange(d, w.p0, 1));
-  dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
-    launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
-                  w.p1, w.Ap, x, w.st, w.partials, d->scal + 0);
-  });
+  if (d->allgather) { // the block with its global columns over the full-length copy of p (column panels as on one GPU)
+    launch_panel_partials(A, lc, s, d->pfull, w.Ap, w.st);
+    const CsrView Vf = csr_view_final(A, w.Ap);
+    const double *gather = d->pfull;
+    dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
+      launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, Vf, (const double *)w.r, w.p0,
+                    w.p1, w.Ap, x, w.st, w.partials, d->scal + 0, gather);
+    });
+  } else {
+    dispatch_lanes(lc.lanes, lc.eng, [&](auto Lc, auto Tc) {
+      launch_kernel(cg_spmv_kernel<decltype(Lc)::value, decltype(Tc)::value, false>, lc, s, V, (const double *)w.r, w.p0,
+                    w.p1, w.Ap, x, w.st, w.partials, d->scal + 0, (const double *)nullptr);
+    });
+  }
   if (d->peer) { // halo correction + all-reduce(p.Ap) + alpha, then r update + all-reduce(r.r) + state advance
     CGB_TRY(peer_halo_apply(d, w.Ap, w.p0, d->scal + 0, 1, 1));
     peer_update_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, d->pctx());
@@ -488,7 +575,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   CGB_CUDA(cudaMemsetAsync(w.p0, 0, sizeof(double) * (size_t)std::max<int64_t>(n, 1), s));
   // K0: r = b - A x0 (halo of x0 first), rr = allreduce(r.r)
   CGB_TRY(halo_exchange(d, d_x, 0));
-  if (n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
+  if (n > 0) CGB_TRY(cgb_spmv(ctx, A, d->allgather ? d->pfull : d_x, w.Ap));
   CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
   if (d->peer) {
     peer_init_kernel<<<A->grid_vec, kBlock, 0, s>>>(n, d_b, w.Ap, w.r, w.st, w.partials, w.hist, d->pctx());
@@ -500,7 +587,9 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   }
   CGB_CUDA(cudaGetLastError());
 
-  const int per_iter = d->peer ? 5 : 6; // kernels of ours per iteration (NCCL's own kernels not counted)
+  // kernels of ours per iteration (NCCL's own kernels not counted); all-gather mode: p-update, all-gather, flag wait,
+  // one SpMV launch per column panel, all-reduce(p.Ap), update
+  const int per_iter = d->allgather ? 5 + (int)std::max<size_t>(1, csr_panels(A)) : d->peer ? 5 : 6;
   int64_t launches = d->peer ? 4 : 5;
   const uint64_t gkey = ((uint64_t)batch << 1) | (d->peer ? 1u : 0u);
   if (persistent) { // the whole loop, the last x update included, in one cooperative kernel (dist_persistent.cuh)
@@ -592,7 +681,7 @@ int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double 
     CGB_TRY(all_agree(d, 1, &all));
   }
   CGB_TRY(halo_exchange(d, d_x, 0));
-  if (A->n > 0) CGB_TRY(cgb_spmv(ctx, A, d_x, w.Ap));
+  if (A->n > 0) CGB_TRY(cgb_spmv(ctx, A, d->allgather ? d->pfull : d_x, w.Ap));
   CGB_TRY(halo_apply(d, w.Ap, nullptr, nullptr, nullptr, 0));
   if (d->peer) {
     peer_resid_kernel<<<A->grid_vec, kBlock, 0, s>>>(A->n, d_b, w.Ap, d_x, w.st, w.partials, d->scal + 8, d->pctx());

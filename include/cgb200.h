@@ -298,6 +298,10 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
                       const cgb_cg_opts *opts, cgb_cg_stats *stats);
 int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double *rr, double *xx);
 int64_t cgb_dist_halo_count(const cgb_dist *d);
+/* How the gathered vector travels for the current matrix: 0 = halo exchange (only the boundary entries the rank's
+ * rows touch: stencils), 1 = all-gather (every rank stores its whole slice into every rank's full-length copy over
+ * NVLink; chosen when a rank needs most of the remote entries anyway: random matrices).  CGB_DIST_ALLGATHER=0/1 forces it. */
+int cgb_dist_exchange_mode(const cgb_dist *d);
 
 /* Host-only halo plan (no GPU needed; used by the CPU tests of the partitioning logic):
  * given a local row block with GLOBAL column indices, returns the sorted distinct remote

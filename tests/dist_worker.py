@@ -58,6 +58,9 @@ def main():
         stencil = not name.startswith("rspd")
         if expect == "persistent" and name in ("p3d7_24", "p2d_64"):   # (a 27-point block one plane thick is mostly halo: it keeps the graph loop)
             assert st["loop_mode"] == L.LOOP_PERSISTENT, st
+        if name.startswith("rspd") and os.environ.get("CGB_DIST_TRANSPORT", "") != "nccl":
+            want_mode = 0 if os.environ.get("CGB_DIST_ALLGATHER", "") == "0" else 1   # dense coupling: all-gather unless switched off
+            assert ctx.lib.cgb_dist_exchange_mode(dcg.h) == want_mode, (name, want_mode)
         if expect == "graph":
             assert st["loop_mode"] == L.LOOP_GRAPH, st
         if os.environ.get("CGB_DIST_JITTER_NS") and stencil:   # bitwise reproducible whatever the timing

@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("variant", ["default", "jitter", "graph", "halo_engine", "nccl", "dict"])
+@pytest.mark.parametrize("variant", ["default", "jitter", "graph", "halo_engine", "no_allgather", "nccl", "dict"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_dist_solve_matches_oracle(world, variant):
     if L.load().cgb_device_count() < world:
@@ -28,6 +28,8 @@ def test_dist_solve_matches_oracle(world, variant):
     if variant == "graph":
         env["CGB_DIST_PERSISTENT"] = "0"          # the launch-per-kernel loop (CUDA-graph batches) stays correct
         env["CGB_TEST_EXPECT_LOOP"] = "graph"
+    if variant == "no_allgather":
+        env["CGB_DIST_ALLGATHER"] = "0"           # the random matrix through the halo split (default for it: all-gather of p)
     if variant == "halo_engine":
         env["CGB_HALO_ENGINE_MIN"] = "1"      # A_halo through the regular row engines even for these small cases
     if variant == "nccl":

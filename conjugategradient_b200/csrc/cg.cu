@@ -41,6 +41,7 @@ struct LoopCfg {
   bool jacobi;     // Jacobi-preconditioned variants of the vector kernels
   bool replace;    // residual replacement at the end of every batch
   const double *b; // right-hand side (replacement only)
+  bool vec_tma;    // TMA-staged p-update / r-update kernels (vec_tma.cuh)
 };
 
 // Enqueue one CG iteration on `s`.  When `timed`, bracket the kernels with external event records
@@ -53,6 +54,8 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
   };
   CGB_CUDA(mark(0));
   if (c.jacobi) cg_pupdate_jacobi_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.dinv, w.p0, x, w.st);
+  else if (!c.fused && c.vec_tma)
+    cg_pupdate_tma_kernel<<<A->grid_pup_tma, kTmaThreads, vec_tma_smem_bytes(3), s>>>(A->n, w.r, w.p0, x, w.st);
   else if (!c.fused) cg_pupdate_kernel<<<c.grid_pup, kBlock, 0, s>>>(A->n, w.r, w.p0, x, w.st);
   CGB_CUDA(mark(1));
   launch_panel_partials(A, c.sl, s, w.p0, w.Ap, w.st); // column panels 0 .. P-2: Ap accumulates
@@ -68,6 +71,8 @@ static int enqueue_iteration(cgb_csr *A, double *x, const LoopCfg &c, cudaStream
   });
   CGB_CUDA(mark(2));
   if (c.jacobi) cg_update_jacobi_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.dinv, w.st, w.partials, w.hist);
+  else if (c.vec_tma)
+    cg_update_tma_kernel<<<A->grid_vec_tma, kTmaThreads, vec_tma_smem_bytes(2), s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist);
   else cg_update_kernel<<<c.grid_vec, kBlock, 0, s>>>(A->n, w.r, w.Ap, w.st, w.partials, w.hist, (const double *)nullptr,
                                                       (double *)nullptr);
   CGB_CUDA(mark(3));
@@ -296,7 +301,8 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
       return fail(CGB_ERR_UNSUPPORTED, "Jacobi preconditioner: a row has no non-zero diagonal entry");
     }
   }
-  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, jacobi, replace, d_b};
+  LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, jacobi, replace, d_b,
+              A->vec_tma && !jacobi && ((uintptr_t)d_x & 15) == 0};
   const char *l2mode = getenv("CGB_L2_WINDOW_MODE");
   if (l2w && !(l2mode && !strcmp(l2mode, "k1"))) { // (k1: the window rides on the SpMV graph nodes only)
     cudaStreamAttrValue v;
@@ -395,7 +401,7 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   if (mode == CGB_LOOP_GRAPH) {
     const uint64_t key = ((uint64_t)batch << 32) ^ ((uint64_t)cfg.sl.lanes << 8) ^ ((uint64_t)fused << 1) ^
                          (uint64_t)cfg.time_kernels ^ ((uint64_t)cfg.sl.grid << 16) ^ ((uint64_t)cfg.sl.eng << 2) ^
-                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)replace << 5) ^ ((uint64_t)jacobi << 6) ^ ((uint64_t)csr_panels(A) << 48);
+                         ((uint64_t)cfg.l2_window << 4) ^ ((uint64_t)replace << 5) ^ ((uint64_t)jacobi << 6) ^ ((uint64_t)cfg.vec_tma << 7) ^ ((uint64_t)csr_panels(A) << 48);
     CGB_TRY(build_graph(A, d_x, cfg, batch, key));
   }
   // Batches are issued one ahead of the poll so the device never waits for the host; kernels of an

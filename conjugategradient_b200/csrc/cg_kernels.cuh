@@ -21,6 +21,7 @@
 #pragma once
 #include "spmv_dict.cuh"
 #include "spmv_tma.cuh"
+#include "vec_tma.cuh"
 
 namespace cgb {
 
@@ -158,6 +159,15 @@ static __global__ void __launch_bounds__(kBlock) cg_pupdate_kernel(int64_t n, co
   }
 }
 
+// K3 with TMA-staged tiles (vec_tma.cuh): kTmaThreads threads, vec_tma_smem_bytes(3) of dynamic shared memory.  Same
+// arithmetic, element for element; chosen for vectors long enough to fill the two-stage pipeline (csr_plan).
+static __global__ void __launch_bounds__(kTmaThreads) cg_pupdate_tma_kernel(int64_t n, const double *r, double *p, double *x,
+                                                                           const CgState *st) {
+  if (!cg_active(st)) return;
+  extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
+  vec_tma_pupdate(n, r, p, x, st->alpha, st->beta, cgb_dyn_smem);
+}
+
 // ---- K1 -------------------------------------------------------------------------------------
 // FUSED: p buffers ping-pong on the iteration parity; p_old = pbuf[iter & 1], p_new = pbuf[~iter & 1].
 template <int L, int ENG, bool FUSED>
@@ -263,6 +273,21 @@ static __global__ void __launch_bounds__(kBlock) cg_update_kernel(int64_t n, dou
         *local_out = rr_new;
       }
     }
+  }
+}
+
+// K2 with TMA-staged tiles (single GPU: alpha from the state, the last CTA advances the state).
+static __global__ void __launch_bounds__(kTmaThreads) cg_update_tma_kernel(int64_t n, double *r, const double *Ap, CgState *st,
+                                                                          double *partials, double *hist) {
+  if (!cg_active(st)) return;
+  extern __shared__ __align__(128) unsigned char cgb_dyn_smem[];
+  __shared__ double red[32];
+  double acc = vec_tma_update(n, r, Ap, st->alpha, cgb_dyn_smem);
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (publish_and_elect(&st->ticket, gridDim.x)) {
+    const double rr_new = reduce_partials(partials, gridDim.x, red);
+    if (threadIdx.x == 0) cg_advance_state(st, rr_new, hist);
   }
 }
 

@@ -330,7 +330,7 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   // of the matrix ("if the union of needed remote columns is >~ half of n, all-gather p").
   {
     const int64_t n_global = d->row_starts[d->nranks];
-    int want = d->peer && n_global - n > 0 && (double)H >= 0.5 * (double)(n_global - n) && nnz_halo * 2 > (int64_t)A->nnz / 2;
+    int want = d->peer && n_global - n > 0 && (double)H >= 0.5 * (double)(n_global - n);
     if (const char *e = getenv("CGB_DIST_ALLGATHER")) want = d->peer && atoi(e) != 0;
     int all = 0;
     CGB_TRY(all_agree(d, want, &all));
@@ -597,6 +597,16 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     launches += 1;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaStreamSynchronize(s));
+    if (getenv("CGB_DIST_TIMING") && d->rank == 0 && w.h_st[0].iter > 0) { // where a trip's time goes, as CTA 0 saw it
+      DistBar hb;
+      CGB_CUDA(cudaMemcpy(&hb, d->bar, sizeof(hb), cudaMemcpyDeviceToHost));
+      static const char *nm[8] = {"p-update", "barrier", "pack+flags", "SpMV local", "barrier", "halo rows", "all-reduce p.Ap", "r-update + all-reduce r.r"};
+      double tot = 0;
+      for (int k = 0; k < 8; k++) tot += (double)hb.phase_ns[k];
+      fprintf(stderr, "[cgb dist timing] persistent loop, %lld trips, CTA 0 of rank 0, us per trip:", (long long)w.h_st[0].iter);
+      for (int k = 0; k < 8; k++) fprintf(stderr, " %s %.1f |", nm[k], 1e-3 * (double)hb.phase_ns[k] / (double)w.h_st[0].iter);
+      fprintf(stderr, " total %.1f\n", 1e-3 * tot / (double)w.h_st[0].iter);
+    }
   }
   if (!persistent && use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != gkey)) {
     if (w.graph) {

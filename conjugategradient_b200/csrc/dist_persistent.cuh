@@ -29,11 +29,16 @@
 // comm_error flag, so one failing wait takes every CTA of the rank out of the loop instead of hanging the GPU.
 #pragma once
 
+#include "vec_tma.cuh"
+
+#ifndef CGB_DIST_VEC_TMA
+#define CGB_DIST_VEC_TMA 1 // the two vector passes through TMA-staged tiles (vec_tma.cuh); 0: grid-stride loops of 16-byte loads
+#endif
 #ifndef CGB_DIST_UNROLL_P
-#define CGB_DIST_UNROLL_P 2 // independent 16-byte loads per array and thread in the p-update phase
+#define CGB_DIST_UNROLL_P 1 // independent 16-byte loads per array and thread in the p-update phase (C4 on 2 GPUs: 1 -> 537 it/s, 2 -> 518)
 #endif
 #ifndef CGB_DIST_UNROLL_U
-#define CGB_DIST_UNROLL_U 4 // ... in the r-update phase
+#define CGB_DIST_UNROLL_U 1 // ... in the r-update phase (4 measured together with the 2 above)
 #endif
 
 namespace {
@@ -43,6 +48,7 @@ struct DistBar {                 // device words of the persistent loop, zeroed 
   unsigned long long gen;        // grid barrier: generations completed
   unsigned long long pack;       // CTAs that finished packing (monotone)
   unsigned long long red;        // reduction ticket (monotone)
+  unsigned long long phase_ns[8]; // CGB_DIST_TIMING: time CTA 0 spent in P, barrier, pack, S, barrier, H, reduce+U, reduce (sums over the trips)
 };
 
 struct DistLoopArgs {
@@ -63,23 +69,20 @@ struct DistLoopArgs {
   double *hist;
   DistBar *bar;
   long long timeout_cycles;
+  int vec_tma;                   // the vector passes through TMA-staged tiles (long vectors) or grid-stride loops (short ones)
+  int phase_timing;              // CGB_DIST_TIMING: CTA 0 stamps the phases (globaltimer)
   unsigned jitter_ns;            // CGB_DIST_JITTER_NS (tests): every CTA sleeps a pseudo-random time below this before each phase
 };
 
 struct GatherWeak { // p is rewritten every trip by other CTAs of this very kernel: plain ld.global, ordered by the barrier's acquire
   const double *x;
-  __device__ __forceinline__ double operator()(int c) const {
-    double v;
-    asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(x + c) : "memory");
-    return v;
-  }
+  // an ordinary load: the kernel also WRITES p through another pointer, so the compiler cannot promote it to the
+  // non-coherent path (checked in the SASS: LDG.E.64, no .CONSTANT), and it stays free to schedule the gathers
+  // (an asm volatile with a memory clobber here cost the tile loop its overlap of shared-memory reads and gathers)
+  __device__ __forceinline__ double operator()(int c) const { return x[c]; }
   struct At {
     const double *xr;
-    __device__ __forceinline__ double operator()(int off) const {
-      double v;
-      asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(xr + off) : "memory");
-      return v;
-    }
+    __device__ __forceinline__ double operator()(int off) const { return xr[off]; }
   };
   __device__ __forceinline__ At at(int64_t row) const { return At{x + row}; }
 };
@@ -239,6 +242,19 @@ __device__ __forceinline__ void dist_pupdate_body(int64_t n, const double *r, do
   }
 }
 
+__device__ __forceinline__ unsigned long long dist_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// CTA 0, thread 0: add the time since the last stamp to phase `k`
+#define DIST_STAMP(k)                                                   \
+  if (a.phase_timing && blockIdx.x == 0 && threadIdx.x == 0) {          \
+    const unsigned long long now_ = dist_now_ns();                      \
+    a.bar->phase_ns[k] += now_ - t_phase;                               \
+    t_phase = now_;                                                     \
+  }
+
 // Stress hook for the flag protocols (tests/test_dist_gpu.py, variant "jitter"): CTAs and ranks drift apart at random.
 __device__ __forceinline__ void dist_jitter(const DistLoopArgs &a, unsigned salt) {
   if (a.jitter_ns == 0) return;
@@ -316,34 +332,43 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
   const int64_t n = a.A.n;
   const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
   bool ok = true;
+  unsigned long long t_phase = a.phase_timing ? dist_now_ns() : 0ull;
   while (!done && it < max_iter) {
     // ---- phase P ----
     dist_jitter(a, 4u * (unsigned)it);
-    dist_pupdate_body(n, a.r, a.p, a.x, alpha, beta);
+    if (CGB_DIST_VEC_TMA && a.vec_tma) vec_tma_pupdate(n, a.r, a.p, a.x, alpha, beta, cgb_dyn_smem);
+    else dist_pupdate_body(n, a.r, a.p, a.x, alpha, beta);
+    DIST_STAMP(0)
     if (!dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
+    DIST_STAMP(1)
     dist_jitter(a, 4u * (unsigned)it + 1u);
     // ---- pack: boundary entries of p to their owners, flags by the CTA that finishes last ----
     halo_seq += 1ull;
-    for (int64_t k = gtid; k < a.S; k += nthr) {
-      int q = 0;
-      while (k >= a.ps.soff[q + 1]) q++;
-      double v;
-      asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(a.p + a.send_idx[k]) : "memory");
-      a.ps.dst[q][k - a.ps.soff[q]] = v;
+    {
+      // only as many CTAs as the send list needs (4 entries per thread) take part in the pack and its ticket; the
+      // others go straight to their tiles
+      const int64_t per_cta = (int64_t)blockDim.x * 4;
+      const int pack_ctas = (int)min((int64_t)gridDim.x, (a.S + per_cta - 1) / per_cta);
+      if ((int)blockIdx.x < pack_ctas) {
+        for (int64_t k = gtid; k < a.S; k += (int64_t)pack_ctas * blockDim.x) {
+          int q = 0;
+          while (k >= a.ps.soff[q + 1]) q++;
+          a.ps.dst[q][k - a.ps.soff[q]] = a.p[a.send_idx[k]];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          __threadfence_system(); // cumulative: the whole CTA's peer stores are ordered before the ticket
+          const unsigned long long t = atomicAdd(&a.bar->pack, 1ull) + 1ull;
+          s_flag = (t == npack + (unsigned long long)pack_ctas);
+          if (s_flag) __threadfence_system(); // acquire side of the ticket: every CTA's stores precede the flags below
+        }
+        __syncthreads();
+        if (s_flag && threadIdx.x < a.pc.nranks && a.ps.soff[threadIdx.x + 1] > a.ps.soff[threadIdx.x])
+          st_release_sys_u64(&win[threadIdx.x]->hflag[a.pc.rank], halo_seq);
+      }
+      npack += (unsigned long long)pack_ctas;
     }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const unsigned long long t = atomicAdd(&a.bar->pack, 1ull) + 1ull;
-      s_flag = (t == (npack + 1ull) * gridDim.x);
-      if (s_flag) __threadfence_system(); // acquire side of the ticket: every CTA's stores precede the flags below
-    }
-    npack += 1ull;
-    __syncthreads();
-    if (s_flag && threadIdx.x < a.pc.nranks && a.ps.soff[threadIdx.x + 1] > a.ps.soff[threadIdx.x]) {
-      __threadfence_system();
-      st_release_sys_u64(&win[threadIdx.x]->hflag[a.pc.rank], halo_seq);
-    }
+    DIST_STAMP(2)
     // ---- phase S: local rows through the TMA tile engine ----
     double a0 = 0.0, a1 = 0.0;
     {
@@ -352,7 +377,9 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
       spmv_rows_tma<L>(a.A.n, a.A.nnz, a.A.rowptr, a.A.cols, a.A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
       spmv_tma_teardown(cgb_dyn_smem, kTmaConsumers / L);
     }
+    DIST_STAMP(3)
     if (!dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
+    DIST_STAMP(4)
     dist_jitter(a, 4u * (unsigned)it + 2u);
     // ---- phase H: halo rows once the neighbours' entries are here ----
     if (a.nh > 0) {
@@ -363,22 +390,42 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
       }
       __syncthreads();
       if (!s_flag) { ok = false; break; }
-      for (int64_t k = gtid; k < a.nh; k += nthr) {
-        double s = 0.0;
-        for (int j = a.h_rowptr[k], e = a.h_rowptr[k + 1]; j < e; j++) s = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s);
-        const int row = a.halo_rows[k];
-        a.Ap[row] += s;
-        a0 = fma(a.p[row], s, a0);
+      // HU rows per thread at a time: the chain row offsets -> column -> halo entry is three dependent round trips,
+      // and a stencil slab has only a few boundary rows per thread
+      constexpr int HU = 2;
+      for (int64_t k0 = gtid; k0 < a.nh; k0 += HU * nthr) {
+        int jb[HU], je[HU], row[HU];
+#pragma unroll
+        for (int u = 0; u < HU; u++) {
+          const int64_t k = k0 + u * nthr;
+          const bool in = k < a.nh;
+          jb[u] = in ? a.h_rowptr[k] : 0;
+          je[u] = in ? a.h_rowptr[k + 1] : 0;
+          row[u] = in ? a.halo_rows[k] : 0;
+        }
+        double s4[HU] = {};
+#pragma unroll
+        for (int u = 0; u < HU; u++)
+          for (int j = jb[u]; j < je[u]; j++) s4[u] = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s4[u]);
+#pragma unroll
+        for (int u = 0; u < HU; u++)
+          if (k0 + u * nthr < a.nh) {
+            a.Ap[row[u]] += s4[u];
+            a0 = fma(a.p[row[u]], s4[u], a0);
+          }
       }
     }
+    DIST_STAMP(5)
     const double pAp = dist_allreduce(a0, a, win, nred, red_seq, red, slots, &ok);
     if (!ok) break;
+    DIST_STAMP(6)
     alpha = rr / pAp; // src/CG.hpp:385-386
     // ---- phase U ----
     dist_jitter(a, 4u * (unsigned)it + 3u);
-    const double acc = dist_update_body(n, a.r, a.Ap, alpha);
+    const double acc = (CGB_DIST_VEC_TMA && a.vec_tma) ? vec_tma_update(n, a.r, a.Ap, alpha, cgb_dyn_smem) : dist_update_body(n, a.r, a.Ap, alpha);
     const double rr_new = dist_allreduce(acc, a, win, nred, red_seq, red, slots, &ok);
     if (!ok) break;
+    DIST_STAMP(7)
     if (isnan(rr) || sqrt(rr) <= tol) { // the rr from BEFORE this trip's update (one-trip lag, src/CG.hpp:396-404)
       done = 1;
       nan_stop = isnan(rr) ? 1 : 0;
@@ -469,6 +516,11 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   a.hist = w.hist;
   a.bar = static_cast<DistBar *>(d->bar);
   a.timeout_cycles = timeout_cycles;
+  // TMA-staged vector passes want >= 8 tiles per CTA (C4 on 2 GPUs: 570 against 547 it/s; C2 on 2 GPUs, 2 tiles per
+  // CTA: 15.7k against 17.6k); CGB_VEC_TMA=0/1 forces it
+  a.vec_tma = A->n >= (int64_t)grid * 8 * kVecTile;
+  if (const char *e = getenv("CGB_VEC_TMA")) a.vec_tma = atoi(e) != 0;
+  a.phase_timing = getenv("CGB_DIST_TIMING") != nullptr;
   if (const char *e = getenv("CGB_DIST_JITTER_NS")) a.jitter_ns = (unsigned)std::max(0, atoi(e));
   CGB_CUDA(cudaMemsetAsync(d->bar, 0, sizeof(DistBar), s));
   void *args[] = {&a};

@@ -49,6 +49,9 @@ struct cgb_csr {
   int grid_spmv = 0;   // CTAs for SpMV-shaped kernels
   int grid_vec = 0;    // CTAs for the x/r update (+ r.r) kernel: one resident wave
   int grid_pup = 0;    // CTAs for the p-update / x-flush kernels: one resident wave
+  // TMA-staged vector passes (vec_tma.cuh) for the p-update and the r-update when the vectors are long enough
+  bool vec_tma = false;
+  int grid_pup_tma = 0, grid_vec_tma = 0;
   bool use_tma = true; // TMA-staged row engine (spmv_tma.cuh) instead of direct loads
   int lanes_tma = 1;   // lanes per row of the TMA engine (tile = 256 / lanes_tma rows)
   int grid_tma = 0;

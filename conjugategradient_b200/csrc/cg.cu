@@ -304,6 +304,10 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   LoopCfg cfg{fused, l2w, o.time_kernels != 0, spmv_launch_cfg(A), A->grid_vec, A->grid_pup, jacobi, replace, d_b,
               A->vec_tma && !jacobi && ((uintptr_t)d_x & 15) == 0};
   const char *l2mode = getenv("CGB_L2_WINDOW_MODE");
+  if (cfg.vec_tma) { // (static kernels: this translation unit's own instances need their shared-memory limit raised)
+    CGB_CUDA(cudaFuncSetAttribute(cg_pupdate_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vec_tma_smem_bytes(3)));
+    CGB_CUDA(cudaFuncSetAttribute(cg_update_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vec_tma_smem_bytes(2)));
+  }
   if (l2w && !(l2mode && !strcmp(l2mode, "k1"))) { // (k1: the window rides on the SpMV graph nodes only)
     cudaStreamAttrValue v;
     memset(&v, 0, sizeof(v));

@@ -242,6 +242,27 @@ __device__ __forceinline__ void dist_pupdate_body(int64_t n, const double *r, do
   }
 }
 
+// Second half of the halo pack, run by an idle lane of the TMA engine's producer warp while the tiles stream: order the
+// CTA's peer stores (they precede the CTA barrier that opened the tile loop, so this thread's fence is cumulative over
+// them), take the ticket, and in the CTA that finishes last raise this rank's flag in every destination window.
+struct PackFinish {
+  bool active;
+  unsigned long long target, seq;
+  DistBar *bar;
+  PeerWin *const *win;
+  const PeerSend *ps;
+  int rank, nranks;
+  __device__ __forceinline__ void operator()() const {
+    if (!active) return;
+    __threadfence_system();
+    const unsigned long long t = atomicAdd(&bar->pack, 1ull) + 1ull;
+    if (t != target) return;
+    __threadfence_system(); // acquire side of the ticket: every CTA's stores precede the flags
+    for (int q = 0; q < nranks; q++)
+      if (ps->soff[q + 1] > ps->soff[q]) st_release_sys_u64(&win[q]->hflag[rank], seq);
+  }
+};
+
 __device__ __forceinline__ unsigned long long dist_now_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -344,29 +365,24 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
     dist_jitter(a, 4u * (unsigned)it + 1u);
     // ---- pack: boundary entries of p to their owners, flags by the CTA that finishes last ----
     halo_seq += 1ull;
+    bool pack_cta;
+    unsigned long long pack_target;
     {
       // only as many CTAs as the send list needs (4 entries per thread) take part in the pack and its ticket; the
       // others go straight to their tiles
       const int64_t per_cta = (int64_t)blockDim.x * 4;
       const int pack_ctas = (int)min((int64_t)gridDim.x, (a.S + per_cta - 1) / per_cta);
-      if ((int)blockIdx.x < pack_ctas) {
+      pack_cta = (int)blockIdx.x < pack_ctas;
+      pack_target = npack + (unsigned long long)pack_ctas;
+      if (pack_cta)
         for (int64_t k = gtid; k < a.S; k += (int64_t)pack_ctas * blockDim.x) {
           int q = 0;
           while (k >= a.ps.soff[q + 1]) q++;
           a.ps.dst[q][k - a.ps.soff[q]] = a.p[a.send_idx[k]];
         }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          __threadfence_system(); // cumulative: the whole CTA's peer stores are ordered before the ticket
-          const unsigned long long t = atomicAdd(&a.bar->pack, 1ull) + 1ull;
-          s_flag = (t == npack + (unsigned long long)pack_ctas);
-          if (s_flag) __threadfence_system(); // acquire side of the ticket: every CTA's stores precede the flags below
-        }
-        __syncthreads();
-        if (s_flag && threadIdx.x < a.pc.nranks && a.ps.soff[threadIdx.x + 1] > a.ps.soff[threadIdx.x])
-          st_release_sys_u64(&win[threadIdx.x]->hflag[a.pc.rank], halo_seq);
-      }
       npack += (unsigned long long)pack_ctas;
+      // the stores are on their way; the fence that orders them, the ticket and the flags run on an idle lane of the
+      // producer warp while the tiles stream (PackFinish below), behind the CTA barrier that opens the tile loop
     }
     DIST_STAMP(2)
     // ---- phase S: local rows through the TMA tile engine ----
@@ -374,7 +390,8 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
     {
       GatherWeak g{a.p};
       EpiDotP e{a.Ap, a.p};
-      spmv_rows_tma<L>(a.A.n, a.A.nnz, a.A.rowptr, a.A.cols, a.A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem);
+      const PackFinish side{pack_cta, pack_target, halo_seq, a.bar, win, &a.ps, a.pc.rank, a.pc.nranks};
+      spmv_rows_tma<L>(a.A.n, a.A.nnz, a.A.rowptr, a.A.cols, a.A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem, side);
       spmv_tma_teardown(cgb_dyn_smem, kTmaConsumers / L);
     }
     DIST_STAMP(3)

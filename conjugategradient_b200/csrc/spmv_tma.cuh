@@ -110,12 +110,18 @@ __device__ __forceinline__ double row_sum_direct(const double *__restrict__ vals
   return sum;
 }
 
+struct TmaNoSideJob {
+  __device__ __forceinline__ void operator()() const {}
+};
+
 // Must be called by all kTmaThreads threads of the CTA.  `smem_raw` is the dynamic shared memory.
-template <int L, class G, class E>
+// `side` runs once on the second lane of the producer warp (which is otherwise idle) while the tiles stream: the
+// persistent multi-GPU loop hides the system-scope fence and the flag stores of its halo pack there.
+template <int L, class G, class E, class SIDE = TmaNoSideJob>
 __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int *__restrict__ rowptr,
                                               const int *__restrict__ cols, const double *__restrict__ vals,
                                               const G &g, const E &e, int bid, int nb, double &a0, double &a1,
-                                              unsigned char *smem_raw) {
+                                              unsigned char *smem_raw, const SIDE &side = SIDE()) {
   constexpr int TILE_ROWS = kTmaConsumers / L;
   constexpr size_t STAGE = tma_stage_bytes(TILE_ROWS);
   unsigned char *base = smem_raw;
@@ -136,6 +142,7 @@ __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int 
   __syncthreads();
 
   if (tid >= kTmaConsumers) {
+    if (tid == kTmaConsumers + 1) side();
     // ---------------- producer warp: one lane drives the TMA ----------------
     if (tid == kTmaConsumers) {
       const uint64_t pol = l2_policy_evict_first();

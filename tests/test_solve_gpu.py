@@ -393,3 +393,31 @@ def test_jacobi_preconditioner_option(ctx):
     with pytest.raises(L.CgbError) as e:
         bad.solve(1e-8)
     assert e.value.code == L.CGB_ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("name", ["p3d7_40", "C1_p2d_128", "rspd_50000"])
+def test_tma_staged_vector_kernels(ctx, port, name, monkeypatch):
+    """The p-update and the r-update as TMA-staged kernels (vec_tma.cuh; what long vectors use: C3, C4, C5) forced onto small
+    systems whose sizes are no multiple of the 1,152-element tile: same trips, same x, bitwise the same r.r history as the
+    grid-stride kernels (the arithmetic per element is identical; only the order of the r.r partial sums differs)."""
+    gen, rel = CASES[name]
+    v, c, r = gen()
+    n = r.size - 1
+    b = G.default_rhs(n)
+    tol = rel * np.linalg.norm(b)
+    o = port.cg_solve(v, c, r, b, tol)
+    monkeypatch.setenv("CGB_VEC_TMA", "0")
+    cg0, st0 = run(ctx, v, c, r, b, tol, loop_mode=L.LOOP_GRAPH, record_history=1)
+    monkeypatch.setenv("CGB_VEC_TMA", "1")          # read when the matrix handle is planned
+    cg1, st1 = run(ctx, v, c, r, b, tol, loop_mode=L.LOOP_GRAPH, record_history=1)
+    slack = 0.05 if name.startswith("rspd") else 0.02
+    assert abs(st1["iterations"] - o["iterations"]) <= max(1, round(slack * o["iterations"])) and st1["converged"] == 1
+    if not name.startswith("rspd"):
+        assert rel_err(cg1.extract(), o["x"]) <= X_RTOL
+        assert st1["iterations"] == st0["iterations"]
+    k = min(cg0.history().size, cg1.history().size, 25)
+    assert np.allclose(cg1.history()[:k], cg0.history()[:k], rtol=1e-12, atol=0)
+    x1 = cg1.extract().copy()
+    cg1.x = None
+    st2 = cg1.solve(tol)                                # deterministic
+    assert st2["iterations"] == st1["iterations"] and np.array_equal(cg1.extract(), x1)

@@ -547,19 +547,32 @@ __global__ void __launch_bounds__(kBlock) peer_resid_kernel(int64_t n, const dou
 }
 
 // All-gather mode: this rank's slice of `vec` goes into every rank's full-length copy (coalesced 16-byte NVLink stores),
-// the last CTA raises this rank's flag in every window.
+// the last CTA raises this rank's flag in every window.  The slice starts at this rank's first row, which may be odd:
+// the 16-byte stores then start one entry in (the buffers themselves are 2 MiB aligned, so all copies agree).
 __global__ void __launch_bounds__(kBlock) peer_allgather_kernel(int64_t n, const double *__restrict__ vec, PeerGather pg,
                                                                  PeerCtx pc, CgState *st, int gated) {
   if (gated && !cg_active(st)) return;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
-  const int64_t n2 = n >> 1;
-  const double2 *v2 = reinterpret_cast<const double2 *>(vec);
-  for (int64_t i = tid; i < n2; i += nthr) {
-    const double2 v = v2[i];
-    for (int q = 0; q < pc.nranks; q++) reinterpret_cast<double2 *>(pg.dst[q])[i] = v;
+  const int64_t head = n > 0 ? (int64_t)((reinterpret_cast<uintptr_t>(pg.dst[pc.rank]) >> 3) & 1) : 0;
+  const int64_t n2 = (n - head) >> 1;
+  if (head == 0) {
+    const double2 *v2 = reinterpret_cast<const double2 *>(vec);
+    for (int64_t i = tid; i < n2; i += nthr) {
+      const double2 v = v2[i];
+      for (int q = 0; q < pc.nranks; q++) reinterpret_cast<double2 *>(pg.dst[q])[i] = v;
+    }
+  } else {
+    for (int64_t i = tid; i < n2; i += nthr) {
+      const double2 v = make_double2(vec[2 * i + 1], vec[2 * i + 2]);
+      for (int q = 0; q < pc.nranks; q++) reinterpret_cast<double2 *>(pg.dst[q] + 1)[i] = v;
+    }
   }
-  if ((n & 1) && tid == 0)
-    for (int q = 0; q < pc.nranks; q++) pg.dst[q][n - 1] = vec[n - 1];
+  if (tid == 0) { // the entry before the first aligned pair and the one after the last
+    for (int q = 0; q < pc.nranks; q++) {
+      if (head) pg.dst[q][0] = vec[0];
+      if (head + 2 * n2 < n) pg.dst[q][n - 1] = vec[n - 1];
+    }
+  }
   __threadfence_system();
   if (publish_and_elect(&st->ticket, gridDim.x)) {
     const unsigned long long s = pc.seq->halo + 1;

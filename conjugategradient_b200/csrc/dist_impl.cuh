@@ -70,6 +70,20 @@ int all_agree(cgb_dist *d, int ok, int *all_ok) {
   return CGB_OK;
 }
 
+// Sums over the ranks of two host numbers (set-up decisions taken on global figures).
+int all_sum2(cgb_dist *d, double a, double b, double *sa, double *sb) {
+  cudaStream_t s = d->ctx->stream;
+  const double v[2] = {a, b};
+  double out[2] = {0.0, 0.0};
+  CGB_CUDA(cudaMemcpyAsync(d->scal + 12, v, sizeof(v), cudaMemcpyHostToDevice, s));
+  CGB_NCCL(g_nccl.AllReduce(d->scal + 12, d->scal + 14, 2, ncclDouble, ncclSum, d->comm, s));
+  CGB_CUDA(cudaMemcpyAsync(out, d->scal + 14, sizeof(out), cudaMemcpyDeviceToHost, s));
+  CGB_CUDA(cudaStreamSynchronize(s));
+  *sa = out[0];
+  *sb = out[1];
+  return CGB_OK;
+}
+
 // CGB_PEER_TIMEOUT_MS (default 30000) in SM clock cycles
 long long peer_timeout_cycles(const cgb_ctx *ctx) {
   double ms = 30000.0;
@@ -330,7 +344,11 @@ int dist_setup(cgb_dist *d, cgb_csr *A) {
   // of the matrix ("if the union of needed remote columns is >~ half of n, all-gather p").
   {
     const int64_t n_global = d->row_starts[d->nranks];
-    int want = d->peer && n_global - n > 0 && (double)H >= 0.5 * (double)(n_global - n);
+    // the figure is global (remote entries needed / remote entries there are, summed over the ranks): a rank with few
+    // rows of its own needs less than half of the rest without that changing what the others have to receive
+    double need = 0.0, there = 0.0;
+    CGB_TRY(all_sum2(d, (double)H, (double)(n_global - n), &need, &there));
+    int want = d->peer && there > 0.0 && need >= 0.5 * there;
     if (const char *e = getenv("CGB_DIST_ALLGATHER")) want = d->peer && atoi(e) != 0;
     int all = 0;
     CGB_TRY(all_agree(d, want, &all));

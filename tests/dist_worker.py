@@ -36,6 +36,9 @@ def main():
         b = G.default_rhs(n)
         tol = rel * np.linalg.norm(b)
         starts = S.partition_rows(n, world, rowptr=r if how == "nnz" else None)
+        if name.startswith("rspd") and world > 1:   # odd first rows: the all-gather's 16-byte stores start one entry in
+            starts = np.asarray(starts).copy()
+            starts[1:-1] |= 1
         lo, hi = int(starts[rank]), int(starts[rank + 1])
         lv, lc, lr = S.local_block(v, c, r, lo, hi)
         A = S.Matrix(ctx, lv, lc, lr)

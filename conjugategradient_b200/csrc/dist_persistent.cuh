@@ -57,6 +57,7 @@ struct DistLoopArgs {
   const int *h_rowptr, *h_cols;  // A_halo (columns index the halo buffer)
   const double *h_vals;
   const int *halo_rows;
+  const int *hperm, *hoff;       // halo rows grouped by the CTA whose tiles hold them (nullptr: grid-stride pass behind a grid barrier)
   const double *halo;
   int64_t S;                     // entries this rank sends
   const int *send_idx;
@@ -395,7 +396,11 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
       spmv_tma_teardown(cgb_dyn_smem, kTmaConsumers / L);
     }
     DIST_STAMP(3)
-    if (!dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
+    // A CTA that has the halo plan adds the halo part to the rows of ITS OWN tiles: Ap there was stored by this CTA's
+    // consumers (visible after the teardown's CTA barrier), so no grid barrier stands between the two phases and a CTA
+    // that is early starts on its halo rows while others still stream tiles.
+    const bool own_rows = a.hperm != nullptr || a.nh == 0;
+    if (!own_rows && !dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
     DIST_STAMP(4)
     dist_jitter(a, 4u * (unsigned)it + 2u);
     // ---- phase H: halo rows once the neighbours' entries are here ----
@@ -410,12 +415,16 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
       // HU rows per thread at a time: the chain row offsets -> column -> halo entry is three dependent round trips,
       // and a stencil slab has only a few boundary rows per thread
       constexpr int HU = 2;
-      for (int64_t k0 = gtid; k0 < a.nh; k0 += HU * nthr) {
+      const int64_t h0 = own_rows ? (int64_t)a.hoff[blockIdx.x] + threadIdx.x : gtid;
+      const int64_t h1 = own_rows ? (int64_t)a.hoff[blockIdx.x + 1] : a.nh;
+      const int64_t hs = own_rows ? (int64_t)blockDim.x : nthr;
+      for (int64_t k0 = h0; k0 < h1; k0 += HU * hs) {
         int jb[HU], je[HU], row[HU];
 #pragma unroll
         for (int u = 0; u < HU; u++) {
-          const int64_t k = k0 + u * nthr;
-          const bool in = k < a.nh;
+          const int64_t kk = k0 + u * hs;
+          const bool in = kk < h1;
+          const int64_t k = !in ? 0 : own_rows ? (int64_t)a.hperm[kk] : kk;
           jb[u] = in ? a.h_rowptr[k] : 0;
           je[u] = in ? a.h_rowptr[k + 1] : 0;
           row[u] = in ? a.halo_rows[k] : 0;
@@ -426,7 +435,7 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
           for (int j = jb[u]; j < je[u]; j++) s4[u] = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s4[u]);
 #pragma unroll
         for (int u = 0; u < HU; u++)
-          if (k0 + u * nthr < a.nh) {
+          if (k0 + u * hs < h1) {
             a.Ap[row[u]] += s4[u];
             a0 = fma(a.p[row[u]], s4[u], a0);
           }
@@ -494,6 +503,61 @@ bool dist_persistent_eligible(const cgb_dist *d, const cgb_cg_opts &o) {
   return true;
 }
 
+// ---- halo rows grouped by owning CTA (tile t of the SpMV engine belongs to CTA t % grid) ----
+__global__ void hplan_key_kernel(int64_t nh, const int *halo_rows, int tile_rows, int grid, int *key, int *val) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nh) return;
+  key[k] = (int)((halo_rows[k] / tile_rows) % grid);
+  val[k] = (int)k;
+}
+__global__ void hplan_off_kernel(int64_t nh, const int *key_sorted, int grid, int *hoff) { // hoff[b] = first k with key >= b
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > grid) return;
+  int64_t lo = 0, hi = nh;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (key_sorted[mid] < b) lo = mid + 1; else hi = mid;
+  }
+  hoff[b] = (int)lo;
+}
+
+struct HplanBuf { // freed on scope exit
+  void *p = nullptr;
+  ~HplanBuf() { cudaFree(p); }
+  template <class T> T *as() { return static_cast<T *>(p); }
+};
+
+int dist_halo_plan(cgb_dist *d, int grid, int tile_rows) {
+  if (d->hperm && d->hplan_grid == grid && d->hplan_tile == tile_rows) return CGB_OK;
+  cudaStream_t s = d->ctx->stream;
+  cudaFree(d->hperm);
+  cudaFree(d->hoff);
+  d->hperm = d->hoff = nullptr;
+  d->hplan_grid = d->hplan_tile = 0;
+  const int64_t nh = d->nh;
+  if (nh <= 0) return CGB_OK;
+  CGB_CUDA(cudaMalloc(&d->hperm, sizeof(int32_t) * (size_t)nh));
+  CGB_CUDA(cudaMalloc(&d->hoff, sizeof(int32_t) * (size_t)(grid + 1)));
+  HplanBuf key, key_s, val, tmp;
+  CGB_CUDA(cudaMalloc(&key.p, sizeof(int) * (size_t)nh));
+  CGB_CUDA(cudaMalloc(&key_s.p, sizeof(int) * (size_t)nh));
+  CGB_CUDA(cudaMalloc(&val.p, sizeof(int) * (size_t)nh));
+  hplan_key_kernel<<<(unsigned)((nh + 255) / 256), 256, 0, s>>>(nh, d->halo_rows, tile_rows, grid, key.as<int>(), val.as<int>());
+  CGB_CUDA(cudaGetLastError());
+  int bits = 1;
+  while ((1 << bits) < grid) bits++;
+  size_t t = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, t, key.as<int>(), key_s.as<int>(), val.as<int>(), d->hperm, (int)nh, 0, bits, s);
+  CGB_CUDA(cudaMalloc(&tmp.p, t + 16));
+  cub::DeviceRadixSort::SortPairs(tmp.p, t, key.as<int>(), key_s.as<int>(), val.as<int>(), d->hperm, (int)nh, 0, bits, s); // stable
+  hplan_off_kernel<<<(unsigned)((grid + 1 + 255) / 256), 256, 0, s>>>(nh, key_s.as<int>(), grid, d->hoff);
+  CGB_CUDA(cudaGetLastError());
+  CGB_CUDA(cudaStreamSynchronize(s));
+  d->hplan_grid = grid;
+  d->hplan_tile = tile_rows;
+  return CGB_OK;
+}
+
 template <int L>
 int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles) {
   cgb_csr *A = d->Aloc;
@@ -519,6 +583,13 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   }
   a.halo_rows = d->halo_rows;
   a.halo = d->halo;
+  bool own_rows = true; // CGB_DIST_OWN_HALO=0: the halo rows as a grid-stride pass behind a grid barrier (A/B)
+  if (const char *e = getenv("CGB_DIST_OWN_HALO")) own_rows = atoi(e) != 0;
+  if (own_rows && d->nh > 0) {
+    CGB_TRY(dist_halo_plan(d, grid, kTmaConsumers / L));
+    a.hperm = d->hperm;
+    a.hoff = d->hoff;
+  }
   a.S = d->S;
   a.send_idx = d->send_idx;
   a.ps = d->send;

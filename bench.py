@@ -108,6 +108,11 @@ class ClockSampler:
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
+        try:  # gone before anything else is timed: a query in flight holds driver locks that launches wait for
+            self.proc.wait(timeout=3)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            self.proc.wait()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ln in self.lines:
@@ -441,13 +446,16 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
     # ---- device-resident solves, default options --------------------------------------------------
     for _ in range(warmup):
         solve_resident()
-    sampler = ClockSampler(rig.local_rank) if headline else None
+    sampler = ClockSampler(rig.local_rank) if headline and not os.environ.get("CGB_BENCH_NO_CLOCKS") else None
     if sampler and rank == 0:
         sampler.start()
     ms_total, outs = rig.timed(solve_resident, steps)
     clocks = sampler.stop() if (sampler and rank == 0) else None
     iters = sum(o["iterations"] for o in outs)
     value = iters / (ms_total / 1e3)
+    if os.environ.get("CGB_BENCH_TRACE") and rank == 0:  # device time inside each solve against the whole timed region
+        print(f"[bench trace] {workload}: timed region {ms_total:.2f} ms, solves " +
+              " ".join(f"{o['solve_ms']:.2f}" for o in outs), file=sys.stderr, flush=True)
     launches = rig.sum_over_ranks(float(sum(o["kernel_launches"] for o in outs)))
     last = outs[-1]
     rr_full, xx_full = residual()  # true residual of the last solve (global)

@@ -72,6 +72,7 @@ struct DistLoopArgs {
   long long timeout_cycles;
   int vec_tma;                   // the vector passes through TMA-staged tiles (long vectors) or grid-stride loops (short ones)
   int phase_timing;              // CGB_DIST_TIMING: CTA 0 stamps the phases (globaltimer)
+  int side_pack;                 // the pack's fence / ticket / flags on the producer warp's idle lane (1) or inline before the tiles (0, A/B)
   unsigned jitter_ns;            // CGB_DIST_JITTER_NS (tests): every CTA sleeps a pseudo-random time below this before each phase
 };
 
@@ -382,6 +383,10 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
           a.ps.dst[q][k - a.ps.soff[q]] = a.p[a.send_idx[k]];
         }
       npack += (unsigned long long)pack_ctas;
+      if (!a.side_pack && pack_cta) { // A/B: finish the pack here, on the critical path
+        __syncthreads();
+        if (threadIdx.x == 0) PackFinish{true, pack_target, halo_seq, a.bar, win, &a.ps, a.pc.rank, a.pc.nranks}();
+      }
       // the stores are on their way; the fence that orders them, the ticket and the flags run on an idle lane of the
       // producer warp while the tiles stream (PackFinish below), behind the CTA barrier that opens the tile loop
     }
@@ -391,7 +396,7 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
     {
       GatherWeak g{a.p};
       EpiDotP e{a.Ap, a.p};
-      const PackFinish side{pack_cta, pack_target, halo_seq, a.bar, win, &a.ps, a.pc.rank, a.pc.nranks};
+      const PackFinish side{pack_cta && a.side_pack, pack_target, halo_seq, a.bar, win, &a.ps, a.pc.rank, a.pc.nranks};
       spmv_rows_tma<L>(a.A.n, a.A.nnz, a.A.rowptr, a.A.cols, a.A.vals, g, e, blockIdx.x, gridDim.x, a0, a1, cgb_dyn_smem, side);
       spmv_tma_teardown(cgb_dyn_smem, kTmaConsumers / L);
     }
@@ -609,6 +614,8 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   a.vec_tma = A->n >= (int64_t)grid * 8 * kVecTile;
   if (const char *e = getenv("CGB_VEC_TMA")) a.vec_tma = atoi(e) != 0;
   a.phase_timing = getenv("CGB_DIST_TIMING") != nullptr;
+  a.side_pack = 1;
+  if (const char *e = getenv("CGB_DIST_SIDE_PACK")) a.side_pack = atoi(e) != 0;
   if (const char *e = getenv("CGB_DIST_JITTER_NS")) a.jitter_ns = (unsigned)std::max(0, atoi(e));
   CGB_CUDA(cudaMemsetAsync(d->bar, 0, sizeof(DistBar), s));
   void *args[] = {&a};

@@ -236,6 +236,9 @@ int cgb_cg_solve(cgb_ctx *ctx, cgb_csr *A, const double *d_b, double *d_x, doubl
   CGB_REQUIRE(d_x, "cgb_cg_solve: x is NULL");
   CGB_REQUIRE(A->ctx == ctx, "cgb_cg_solve: matrix belongs to another context");
   CGB_REQUIRE(((uintptr_t)d_x & 15) == 0, "cgb_cg_solve: x must be 16-byte aligned (128-bit vector accesses)");
+  if (A->n_cols > A->n)
+    return fail(CGB_ERR_INVALID, "cgb_cg_solve: the matrix is not square (%lld rows, column ids up to %lld): rows without entries were "
+                "compacted away (CGB_COO_COMPACT_ROWS, the reference reader's dialect)", (long long)A->n, (long long)A->n_cols);
   cgb_cg_opts o;
   if (opts_in) o = *opts_in; else cgb_cg_default_opts(&o);
   if (stats) memset(stats, 0, sizeof(*stats));

@@ -214,12 +214,9 @@ int coo_to_csr_device(cgb_ctx *ctx, int64_t n_rows, int64_t h, const int *d_r, c
     const int tot32 = (int)total;
     CGB_CUDA(cudaMemcpyAsync(rowptr + n, &tot32, sizeof(int), cudaMemcpyHostToDevice, s));
     CGB_CUDA(cudaStreamSynchronize(s));
-    // The reference dialect drops empty rows but leaves the column ids alone (test/mm_reader.cpp:92-104): with an empty
-    // row the columns reach past the compacted dimension and the reference's spmv reads outside its vector (undefined
-    // behaviour there, a device fault here).  Such a file cannot be an SPD system: refuse it.
-    if (span > n)
-      return fail(CGB_ERR_INVALID, "matrix has %lld empty row(s): column ids reach %lld but only %lld rows hold entries "
-                  "(the reference reader compacts rows without renumbering columns)", (long long)(span - n), (long long)span, (long long)n);
+    // Column ids are left alone (test/mm_reader.cpp:92-104): with an empty row they reach past the compacted dimension
+    // and the result is a rectangular n x span matrix (n_cols below) -- fine for cgb_spmv with a vector of that length,
+    // refused by the solver and by cgb_csr_from_mm_file.
   } else {
     n = n_rows >= 0 ? n_rows : span;
     CGB_CUDA(cudaMalloc(&rowptr, sizeof(int) * (size_t)(n + 1) + 64));
@@ -230,7 +227,7 @@ int coo_to_csr_device(cgb_ctx *ctx, int64_t n_rows, int64_t h, const int *d_r, c
   CGB_CUDA(cudaStreamSynchronize(s));
   CGB_TRY(cgb_csr_from_device(ctx, n, total, ovals, cols, rowptr, 1, out));
   g_cols.p = g_row.p = g_vals.p = nullptr; // owned by the handle now
-  if (!compact && n_rows < 0 && span > n) (*out)->n_cols = span;
+  if (span > n && (compact || n_rows < 0)) (*out)->n_cols = span;
   return CGB_OK;
 }
 
@@ -304,7 +301,17 @@ int cgb_csr_from_mm_file(cgb_ctx *ctx, const char *path, cgb_csr **out) {
     fprintf(stderr, "cgb_csr_from_mm_file: parse %.3f s (%zu chunks), upload + GPU assembly %.3f s (%zu triplets)\n",
             std::chrono::duration<double>(t1 - t0).count(), pr.size(), std::chrono::duration<double>(t2 - t1).count(), total);
   }
-  return rc;
+  if (rc != CGB_OK) return rc;
+  // The reference dialect drops empty rows but leaves the column ids alone: the reference's own spmv would then read
+  // outside its vector (undefined behaviour there, a device fault here).  Such a file cannot be an SPD system: refuse it.
+  if ((*out)->n_cols > (*out)->n) {
+    const long long n = (long long)(*out)->n, span = (long long)(*out)->n_cols;
+    cgb_csr_destroy(*out);
+    *out = nullptr;
+    return fail(CGB_ERR_INVALID, "matrix has %lld empty row(s): column ids reach %lld but only %lld rows hold entries "
+                "(the reference reader compacts rows without renumbering columns)", span - n, span, n);
+  }
+  return CGB_OK;
 }
 
 } // extern "C"

@@ -99,6 +99,13 @@ def test_triplets_flags(ctx):
     C2 = S.Matrix.from_triplets(ctx, rows[keep], c[keep], v[keep], flags=L.COO_COMPACT_ROWS)
     cv, cc, cr = C2.to_host()
     assert cr.size == n - np.count_nonzero(np.arange(n) % 7 == 3) + 1 and same((cv, cc), (hv, hc))
+    # ... which leaves a rectangular matrix (column ids are not renumbered, test/mm_reader.cpp:92-104): the solver refuses it
+    cg = S.CG(ctx)
+    cg.setMatrix(C2)
+    cg.setTarget(np.ones(C2.N()))
+    with pytest.raises(L.CgbError) as e:
+        cg.solve(1e-8)
+    assert e.value.code == L.CGB_ERR_INVALID and "not square" in str(e.value)
     # n = -1: dimension from the largest index
     D = S.Matrix.from_triplets(ctx, rows, c, v)
     assert D.N() == n

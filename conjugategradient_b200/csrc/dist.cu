@@ -128,9 +128,11 @@ struct cgb_dist {
   std::vector<double *> pfull_of;       // peers' copies as mapped here
   PeerGather gather;
   void *bar = nullptr;                  // DistBar of the persistent loop (dist_persistent.cuh)
-  // persistent loop: halo rows grouped by the CTA whose SpMV tiles hold them (hperm: indices into halo_rows, stable
-  // order; hoff[b] .. hoff[b+1]: CTA b's share), valid for this grid size and tile height
-  int32_t *hperm = nullptr, *hoff = nullptr;
+  // persistent loop: halo rows grouped by the CTA whose SpMV tiles hold them, stable order; one int4 per row
+  // {local row, first entry, one past the last entry in A_halo, 1}; hoff[b] .. hoff[b+1]: CTA b's share.  Valid for
+  // this grid size and tile height.
+  int4 *hplan = nullptr;
+  int32_t *hoff = nullptr;
   int hplan_grid = 0, hplan_tile = 0;
   bool dead = false;                    // a peer wait timed out: windows and sequence numbers are inconsistent across ranks
   PeerCtx pctx() const { return PeerCtx{rank, nranks, d_win, seq}; }
@@ -770,9 +772,10 @@ static void dist_release_matrix(cgb_dist *d) {
   cudaFree(d->send_buf);
   cudaFree(d->halo);
   cudaFree(d->pfull);
-  cudaFree(d->hperm);
+  cudaFree(d->hplan);
   cudaFree(d->hoff);
-  d->hperm = d->hoff = nullptr;
+  d->hplan = nullptr;
+  d->hoff = nullptr;
   d->hplan_grid = d->hplan_tile = 0;
   d->pfull = nullptr;
   d->allgather = false;

@@ -615,15 +615,18 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
     launches += 1;
     CGB_CUDA(cudaMemcpyAsync(&w.h_st[0], w.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     CGB_CUDA(cudaStreamSynchronize(s));
-    if (getenv("CGB_DIST_TIMING") && d->rank == 0 && w.h_st[0].iter > 0) { // where a trip's time goes, as CTA 0 saw it
+    const char *tm = getenv("CGB_DIST_TIMING"); // 1: rank 0 prints where a trip's time goes, as its CTA 0 saw it; 2: every rank
+    if (tm && (d->rank == 0 || atoi(tm) >= 2) && w.h_st[0].iter > 0) {
       DistBar hb;
       CGB_CUDA(cudaMemcpy(&hb, d->bar, sizeof(hb), cudaMemcpyDeviceToHost));
-      static const char *nm[8] = {"p-update", "barrier", "pack+flags", "SpMV local", "barrier", "halo rows", "all-reduce p.Ap", "r-update + all-reduce r.r"};
+      static const char *nm[9] = {"p-update", "barrier", "pack", "SpMV local", "halo flag wait", "halo rows", "all-reduce p.Ap", "r-update", "all-reduce r.r"};
       double tot = 0;
-      for (int k = 0; k < 8; k++) tot += (double)hb.phase_ns[k];
-      fprintf(stderr, "[cgb dist timing] persistent loop, %lld trips, CTA 0 of rank 0, us per trip:", (long long)w.h_st[0].iter);
-      for (int k = 0; k < 8; k++) fprintf(stderr, " %s %.1f |", nm[k], 1e-3 * (double)hb.phase_ns[k] / (double)w.h_st[0].iter);
-      fprintf(stderr, " total %.1f\n", 1e-3 * tot / (double)w.h_st[0].iter);
+      for (int k = 0; k < 9; k++) tot += (double)hb.phase_ns[k];
+      char line[640];
+      int off = snprintf(line, sizeof(line), "[cgb dist timing] persistent loop, %lld trips, CTA 0 of rank %d, us per trip:", (long long)w.h_st[0].iter, d->rank);
+      for (int k = 0; k < 9; k++) off += snprintf(line + off, sizeof(line) - (size_t)off, " %s %.1f |", nm[k], 1e-3 * (double)hb.phase_ns[k] / (double)w.h_st[0].iter);
+      snprintf(line + off, sizeof(line) - (size_t)off, " total %.1f\n", 1e-3 * tot / (double)w.h_st[0].iter);
+      fputs(line, stderr); // one write per rank: lines of different ranks do not interleave
     }
   }
   if (!persistent && use_graph && (!w.graph || w.graph_x != d_x || w.graph_key != gkey)) {

@@ -48,7 +48,7 @@ struct DistBar {                 // device words of the persistent loop, zeroed 
   unsigned long long gen;        // grid barrier: generations completed
   unsigned long long pack;       // CTAs that finished packing (monotone)
   unsigned long long red;        // reduction ticket (monotone)
-  unsigned long long phase_ns[8]; // CGB_DIST_TIMING: time CTA 0 spent in P, barrier, pack, S, barrier, H, reduce+U, reduce (sums over the trips)
+  unsigned long long phase_ns[10]; // CGB_DIST_TIMING: time CTA 0 spent in P, barrier, pack, S, (barrier +) halo flag wait, halo rows, all-reduce, U, all-reduce (sums over the trips)
 };
 
 struct DistLoopArgs {
@@ -57,7 +57,8 @@ struct DistLoopArgs {
   const int *h_rowptr, *h_cols;  // A_halo (columns index the halo buffer)
   const double *h_vals;
   const int *halo_rows;
-  const int *hperm, *hoff;       // halo rows grouped by the CTA whose tiles hold them (nullptr: grid-stride pass behind a grid barrier)
+  const int4 *hplan;             // halo rows grouped by the CTA whose tiles hold them: {row, first entry, end, 1} (nullptr: grid-stride
+  const int *hoff;               // pass behind a grid barrier); hoff[b] .. hoff[b+1] = CTA b's share
   const double *halo;
   int64_t S;                     // entries this rank sends
   const int *send_idx;
@@ -244,6 +245,29 @@ __device__ __forceinline__ void dist_pupdate_body(int64_t n, const double *r, do
   }
 }
 
+// Loads of data that every trip reads again and nothing in the kernel writes (halo plan, halo part of the matrix):
+// non-coherent path, L2 evict-last hint so the matrix stream does not push them out between trips.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ int4 ld_keep_int4(const int4 *p, uint64_t pol) {
+  int4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.s32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ double ld_keep_f64(const double *p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ int ld_keep_s32(const int *p, uint64_t pol) {
+  int v;
+  asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+
 // Second half of the halo pack, run by an idle lane of the TMA engine's producer warp while the tiles stream: order the
 // CTA's peer stores (they precede the CTA barrier that opened the tile loop, so this thread's fence is cumulative over
 // them), take the ticket, and in the CTA that finishes last raise this rank's flag in every destination window.
@@ -404,9 +428,8 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
     // A CTA that has the halo plan adds the halo part to the rows of ITS OWN tiles: Ap there was stored by this CTA's
     // consumers (visible after the teardown's CTA barrier), so no grid barrier stands between the two phases and a CTA
     // that is early starts on its halo rows while others still stream tiles.
-    const bool own_rows = a.hperm != nullptr || a.nh == 0;
+    const bool own_rows = a.hplan != nullptr || a.nh == 0;
     if (!own_rows && !dist_grid_barrier(a.bar, gen, st, a.timeout_cycles)) { ok = false; break; }
-    DIST_STAMP(4)
     dist_jitter(a, 4u * (unsigned)it + 2u);
     // ---- phase H: halo rows once the neighbours' entries are here ----
     if (a.nh > 0) {
@@ -417,33 +440,71 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
       }
       __syncthreads();
       if (!s_flag) { ok = false; break; }
-      // HU rows per thread at a time: the chain row offsets -> column -> halo entry is three dependent round trips,
-      // and a stencil slab has only a few boundary rows per thread
+      DIST_STAMP(4)
+      // HU rows per thread at a time.  The pass is a chain of dependent round trips (plan entry -> column and value ->
+      // halo entry) over a few rows per thread: the plan entries of the next round are fetched while this one runs,
+      // the first entry of every row (the only one of a 7-point slab) is issued for all HU rows before any is used,
+      // and plan and matrix part carry an L2 evict-last hint (a few MB that every trip reads again).
       constexpr int HU = 2;
-      const int64_t h0 = own_rows ? (int64_t)a.hoff[blockIdx.x] + threadIdx.x : gtid;
-      const int64_t h1 = own_rows ? (int64_t)a.hoff[blockIdx.x + 1] : a.nh;
-      const int64_t hs = own_rows ? (int64_t)blockDim.x : nthr;
-      for (int64_t k0 = h0; k0 < h1; k0 += HU * hs) {
-        int jb[HU], je[HU], row[HU];
+      if (own_rows) {
+        const uint64_t keep = l2_policy_evict_last();
+        const int64_t h1 = (int64_t)a.hoff[blockIdx.x + 1], hs = (int64_t)blockDim.x;
+        int64_t k0 = (int64_t)a.hoff[blockIdx.x] + threadIdx.x;
+        int4 e[HU];
 #pragma unroll
-        for (int u = 0; u < HU; u++) {
-          const int64_t kk = k0 + u * hs;
-          const bool in = kk < h1;
-          const int64_t k = !in ? 0 : own_rows ? (int64_t)a.hperm[kk] : kk;
-          jb[u] = in ? a.h_rowptr[k] : 0;
-          je[u] = in ? a.h_rowptr[k + 1] : 0;
-          row[u] = in ? a.halo_rows[k] : 0;
-        }
-        double s4[HU] = {};
+        for (int u = 0; u < HU; u++) e[u] = k0 + u * hs < h1 ? ld_keep_int4(a.hplan + k0 + u * hs, keep) : make_int4(0, 0, 0, 0);
+        for (; k0 < h1; k0 += HU * hs) {
+          int4 nx[HU];
 #pragma unroll
-        for (int u = 0; u < HU; u++)
-          for (int j = jb[u]; j < je[u]; j++) s4[u] = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s4[u]);
-#pragma unroll
-        for (int u = 0; u < HU; u++)
-          if (k0 + u * hs < h1) {
-            a.Ap[row[u]] += s4[u];
-            a0 = fma(a.p[row[u]], s4[u], a0);
+          for (int u = 0; u < HU; u++) {
+            const int64_t kn = k0 + (HU + u) * hs;
+            nx[u] = kn < h1 ? ld_keep_int4(a.hplan + kn, keep) : make_int4(0, 0, 0, 0);
           }
+          double v0[HU];
+          int c0[HU];
+#pragma unroll
+          for (int u = 0; u < HU; u++) {
+            const bool ne = e[u].y < e[u].z;
+            v0[u] = ne ? ld_keep_f64(a.h_vals + e[u].y, keep) : 0.0;
+            c0[u] = ne ? ld_keep_s32(a.h_cols + e[u].y, keep) : 0;
+          }
+          double s4[HU];
+#pragma unroll
+          for (int u = 0; u < HU; u++) s4[u] = e[u].y < e[u].z ? fma(v0[u], __ldcg(a.halo + c0[u]), 0.0) : 0.0;
+#pragma unroll
+          for (int u = 0; u < HU; u++)
+            for (int j = e[u].y + 1; j < e[u].z; j++) s4[u] = fma(ld_keep_f64(a.h_vals + j, keep), __ldcg(a.halo + ld_keep_s32(a.h_cols + j, keep)), s4[u]);
+#pragma unroll
+          for (int u = 0; u < HU; u++)
+            if (e[u].w) {
+              a.Ap[e[u].x] += s4[u];
+              a0 = fma(a.p[e[u].x], s4[u], a0);
+            }
+#pragma unroll
+          for (int u = 0; u < HU; u++) e[u] = nx[u];
+        }
+      } else {
+        for (int64_t k0 = gtid; k0 < a.nh; k0 += HU * nthr) {
+          int jb[HU], je[HU], row[HU];
+#pragma unroll
+          for (int u = 0; u < HU; u++) {
+            const int64_t k = k0 + u * nthr;
+            const bool in = k < a.nh;
+            jb[u] = in ? a.h_rowptr[k] : 0;
+            je[u] = in ? a.h_rowptr[k + 1] : 0;
+            row[u] = in ? a.halo_rows[k] : 0;
+          }
+          double s4[HU] = {};
+#pragma unroll
+          for (int u = 0; u < HU; u++)
+            for (int j = jb[u]; j < je[u]; j++) s4[u] = fma(a.h_vals[j], __ldcg(a.halo + a.h_cols[j]), s4[u]);
+#pragma unroll
+          for (int u = 0; u < HU; u++)
+            if (k0 + u * nthr < a.nh) {
+              a.Ap[row[u]] += s4[u];
+              a0 = fma(a.p[row[u]], s4[u], a0);
+            }
+        }
       }
     }
     DIST_STAMP(5)
@@ -454,9 +515,10 @@ __global__ void __launch_bounds__(kTmaThreads, 3) cg_dist_persistent_kernel(cons
     // ---- phase U ----
     dist_jitter(a, 4u * (unsigned)it + 3u);
     const double acc = (CGB_DIST_VEC_TMA && a.vec_tma) ? vec_tma_update(n, a.r, a.Ap, alpha, cgb_dyn_smem) : dist_update_body(n, a.r, a.Ap, alpha);
+    DIST_STAMP(7)
     const double rr_new = dist_allreduce(acc, a, win, nred, red_seq, red, slots, &ok);
     if (!ok) break;
-    DIST_STAMP(7)
+    DIST_STAMP(8)
     if (isnan(rr) || sqrt(rr) <= tol) { // the rr from BEFORE this trip's update (one-trip lag, src/CG.hpp:396-404)
       done = 1;
       nan_stop = isnan(rr) ? 1 : 0;
@@ -526,6 +588,13 @@ __global__ void hplan_off_kernel(int64_t nh, const int *key_sorted, int grid, in
   hoff[b] = (int)lo;
 }
 
+__global__ void hplan_fill_kernel(int64_t nh, const int *perm, const int *halo_rows, const int *h_rowptr, int4 *plan) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nh) return;
+  const int k = perm[j];
+  plan[j] = make_int4(halo_rows[k], h_rowptr[k], h_rowptr[k + 1], 1);
+}
+
 struct HplanBuf { // freed on scope exit
   void *p = nullptr;
   ~HplanBuf() { cudaFree(p); }
@@ -533,17 +602,19 @@ struct HplanBuf { // freed on scope exit
 };
 
 int dist_halo_plan(cgb_dist *d, int grid, int tile_rows) {
-  if (d->hperm && d->hplan_grid == grid && d->hplan_tile == tile_rows) return CGB_OK;
+  if (d->hplan && d->hplan_grid == grid && d->hplan_tile == tile_rows) return CGB_OK;
   cudaStream_t s = d->ctx->stream;
-  cudaFree(d->hperm);
+  cudaFree(d->hplan);
   cudaFree(d->hoff);
-  d->hperm = d->hoff = nullptr;
+  d->hplan = nullptr;
+  d->hoff = nullptr;
   d->hplan_grid = d->hplan_tile = 0;
   const int64_t nh = d->nh;
   if (nh <= 0) return CGB_OK;
-  CGB_CUDA(cudaMalloc(&d->hperm, sizeof(int32_t) * (size_t)nh));
+  CGB_CUDA(cudaMalloc(&d->hplan, sizeof(int4) * (size_t)nh));
   CGB_CUDA(cudaMalloc(&d->hoff, sizeof(int32_t) * (size_t)(grid + 1)));
-  HplanBuf key, key_s, val, tmp;
+  HplanBuf key, key_s, val, perm, tmp;
+  CGB_CUDA(cudaMalloc(&perm.p, sizeof(int) * (size_t)nh));
   CGB_CUDA(cudaMalloc(&key.p, sizeof(int) * (size_t)nh));
   CGB_CUDA(cudaMalloc(&key_s.p, sizeof(int) * (size_t)nh));
   CGB_CUDA(cudaMalloc(&val.p, sizeof(int) * (size_t)nh));
@@ -552,10 +623,11 @@ int dist_halo_plan(cgb_dist *d, int grid, int tile_rows) {
   int bits = 1;
   while ((1 << bits) < grid) bits++;
   size_t t = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, t, key.as<int>(), key_s.as<int>(), val.as<int>(), d->hperm, (int)nh, 0, bits, s);
+  cub::DeviceRadixSort::SortPairs(nullptr, t, key.as<int>(), key_s.as<int>(), val.as<int>(), perm.as<int>(), (int)nh, 0, bits, s);
   CGB_CUDA(cudaMalloc(&tmp.p, t + 16));
-  cub::DeviceRadixSort::SortPairs(tmp.p, t, key.as<int>(), key_s.as<int>(), val.as<int>(), d->hperm, (int)nh, 0, bits, s); // stable
+  cub::DeviceRadixSort::SortPairs(tmp.p, t, key.as<int>(), key_s.as<int>(), val.as<int>(), perm.as<int>(), (int)nh, 0, bits, s); // stable
   hplan_off_kernel<<<(unsigned)((grid + 1 + 255) / 256), 256, 0, s>>>(nh, key_s.as<int>(), grid, d->hoff);
+  hplan_fill_kernel<<<(unsigned)((nh + 255) / 256), 256, 0, s>>>(nh, perm.as<int>(), d->halo_rows, d->Ahalo->rowptr, d->hplan);
   CGB_CUDA(cudaGetLastError());
   CGB_CUDA(cudaStreamSynchronize(s));
   d->hplan_grid = grid;
@@ -592,7 +664,7 @@ int dist_persistent_launch_L(cgb_dist *d, double *d_x, long long timeout_cycles)
   if (const char *e = getenv("CGB_DIST_OWN_HALO")) own_rows = atoi(e) != 0;
   if (own_rows && d->nh > 0) {
     CGB_TRY(dist_halo_plan(d, grid, kTmaConsumers / L));
-    a.hperm = d->hperm;
+    a.hplan = d->hplan;
     a.hoff = d->hoff;
   }
   a.S = d->S;

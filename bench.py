@@ -673,7 +673,11 @@ def run_ours(args):
             if wl == args.workload:
                 continue
             t0 = time.time()
-            r = run_workload(rig, args, wl, 3, 3, 2, min(args.cpu_seconds, 6.0), headline=False)
+            try:
+                r = run_workload(rig, args, wl, 3, 3, 2, min(args.cpu_seconds, 6.0), headline=False)
+            except Exception as e:  # noqa: BLE001 — the headline has been measured: report it, say what failed, stop here
+                others[BASELINE_NAME[wl]] = {"error": f"{type(e).__name__}: {e}"[:400]}
+                break
             entry = {"config": config_dict(wl, r["kind"], r["m"], r["n"], r["nnz"], r["rel"], world), "value": r["value"],
                      "unit": UNIT, "steps": r["steps"], "warmup": r["warmup"], "ms_per_step": r["ms_total"] / r["steps"],
                      "iterations_per_solve": r["run"]["iterations_per_solve"], "true_rel_residual": r["run"]["true_rel_residual"],

@@ -175,6 +175,25 @@ def l2_roofline(nnz, k1_ms, rig):
             "peak_source": "tools/gather_bench.cu, live: random 8-byte gathers out of a 40 MB vector, 32 B sector per gather"}
 
 
+_STREAM_PEAKS = {}
+
+
+def stream_peaks(rig):
+    """HBM rates of this box on the access mixes the CG kernels have (tools/stream_bench.cu, run live once): read only,
+    13 reads : 1 write (the SpMV kernel's mix) and a 1 : 1 copy.  The driver's MEASURED_PEAKS figure is a copy."""
+    exe = os.path.join(ROOT, "tools", "_build", "stream_bench")
+    if "v" not in _STREAM_PEAKS:
+        _STREAM_PEAKS["v"] = None
+        if os.path.exists(exe) and rig.world == 1:
+            try:
+                env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(rig.local_rank))
+                out = subprocess.run([exe, "4", "3"], capture_output=True, text=True, timeout=120, env=env)
+                _STREAM_PEAKS["v"] = json.loads(out.stdout.strip().splitlines()[-1])
+            except Exception:  # noqa: BLE001
+                _STREAM_PEAKS["v"] = None
+    return _STREAM_PEAKS["v"]
+
+
 def golden_parity(workload):
     if os.path.exists(GOLDEN_PARITY):
         return json.load(open(GOLDEN_PARITY)).get(workload)
@@ -528,7 +547,13 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
                     "iteration_frac_of_8TBps": it_gbps / 8000.0,
                     "l2": l2_roofline(nnz, k1_ms, rig) if last["format"] == L.FMT_SELL else None,
                     "note": "frac can exceed 1: the peak is a COPY (half reads, half writes); this kernel's traffic is 93 % reads, "
-                            "which HBM3e serves faster than a 50/50 mix. The spec-based fraction is frac_of_8TBps_spec."}
+                            "which HBM3e serves faster than a 50/50 mix. The spec-based fraction is frac_of_8TBps_spec; "
+                            "stream_peaks holds this box's own rates on the kernel's mix, measured in this run."}
+            if headline:
+                sp = stream_peaks(rig)
+                roof["stream_peaks"] = sp
+                if sp and sp.get("spmv_mix_13r_1w_GBps"):
+                    roof["frac_of_same_mix_stream"] = ach / sp["spmv_mix_13r_1w_GBps"]
 
     # ---- opt-in storage format (not the headline): the same solve through the row-pattern dictionary copy ----
     # (CGB_FMT_DICT, include/cgb200.h: 2 bytes per ROW instead of 12 per non-zero for constant-coefficient stencils;

@@ -548,12 +548,13 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
                     "l2": l2_roofline(nnz, k1_ms, rig) if last["format"] == L.FMT_SELL else None,
                     "note": "frac can exceed 1: the peak is a COPY (half reads, half writes); this kernel's traffic is 93 % reads, "
                             "which HBM3e serves faster than a 50/50 mix. The spec-based fraction is frac_of_8TBps_spec; "
-                            "stream_peaks holds this box's own rates on the kernel's mix, measured in this run."}
+                            "stream_peaks holds this box's own streaming rates measured in this run (tools/stream_bench.cu); "
+                            "frac_of_read_only_stream is against the read-only one, an upper bound for any mix."}
             if headline:
                 sp = stream_peaks(rig)
                 roof["stream_peaks"] = sp
-                if sp and sp.get("spmv_mix_13r_1w_GBps"):
-                    roof["frac_of_same_mix_stream"] = ach / sp["spmv_mix_13r_1w_GBps"]
+                if sp and sp.get("read_only_GBps"):  # the tightest ceiling the probe gives: nothing but reads (LDG.128 or TMA bulk)
+                    roof["frac_of_read_only_stream"] = ach / max(sp["read_only_GBps"], sp.get("read_only_tma_GBps") or 0.0)
 
     # ---- opt-in storage format (not the headline): the same solve through the row-pattern dictionary copy ----
     # (CGB_FMT_DICT, include/cgb200.h: 2 bytes per ROW instead of 12 per non-zero for constant-coefficient stencils;

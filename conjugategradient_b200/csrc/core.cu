@@ -343,8 +343,21 @@ int cgb_ctx_create(int device, cgb_ctx **out) {
                 e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
   }
   if (device < 0 || device >= count) return fail(CGB_ERR_INVALID, "cgb_ctx_create: device %d out of range [0,%d)", device, count);
+  // cudaGetDeviceProperties costs 2-3 ms (and now and then 100 ms: it walks driver state); callers of the reference API
+  // create a solver, and with it a context, per system, so the answer is kept per device for the life of the process
+  static std::mutex prop_mu;
+  static std::map<int, cudaDeviceProp> prop_of;
   cudaDeviceProp prop;
-  CGB_CUDA(cudaGetDeviceProperties(&prop, device));
+  {
+    std::lock_guard<std::mutex> lk(prop_mu);
+    auto it = prop_of.find(device);
+    if (it == prop_of.end()) {
+      CGB_CUDA(cudaGetDeviceProperties(&prop, device));
+      prop_of[device] = prop;
+    } else {
+      prop = it->second;
+    }
+  }
   if (prop.major < 10)
     return fail(CGB_ERR_CUDA, "cgb_ctx_create: device %d is sm_%d%d; this library ships sm_100a code only", device,
                 prop.major, prop.minor);
@@ -361,7 +374,7 @@ int cgb_ctx_create(int device, cgb_ctx **out) {
     delete ctx;
     return fail(CGB_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
   }
-  e = cudaMallocHost(&ctx->pinned, 4096);
+  e = cached_host_alloc((void **)&ctx->pinned, 4096);
   if (e != cudaSuccess) {
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -377,7 +390,7 @@ int cgb_ctx_destroy(cgb_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   if (ctx->partials) cached_free(ctx->partials);
   if (ctx->ticket) cached_free(ctx->ticket);
-  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->pinned) cached_host_free(ctx->pinned);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
   return CGB_OK;

@@ -53,16 +53,26 @@ int main(int argc, char **argv) {
     bb += target[(size_t)i] * target[(size_t)i];
   }
   const double tol = rtol * std::sqrt(bb);
+  const bool trace = std::getenv("E2E_TRACE") != nullptr;
   long long iters = 0, last_iters = 0;
   double seconds = 0.0, device_seconds = 0.0, checksum = 0.0;
   for (int s = 0; s < warmup + steps; s++) {
     const auto t0 = std::chrono::steady_clock::now();
     auto cg = CG<double>::createCG();
+    const auto ta = std::chrono::steady_clock::now();
     cg->setMatrix(data, cols, rows);
+    const auto tb = std::chrono::steady_clock::now();
     cg->setTarget(target);
+    const auto tc = std::chrono::steady_clock::now();
     cg->solve(tol);
+    const auto td = std::chrono::steady_clock::now();
     std::vector<double> x = cg->extract();
     const auto t1 = std::chrono::steady_clock::now();
+    if (trace) { // E2E_TRACE=1: where a step's wall clock goes
+      auto ms = [](auto a, auto b) { return 1e3 * std::chrono::duration<double>(b - a).count(); };
+      std::fprintf(stderr, "[e2e_cpp] step %d: createCG %.2f | setMatrix %.2f | setTarget %.2f | solve %.2f (device %.2f) | extract %.2f | total %.2f ms\n",
+                   s, ms(t0, ta), ms(ta, tb), ms(tb, tc), ms(tc, td), 1e3 * cg->seconds(), ms(td, t1), ms(t0, t1));
+    }
     if (s >= warmup) {
       iters += cg->iterations();
       seconds += std::chrono::duration<double>(t1 - t0).count();

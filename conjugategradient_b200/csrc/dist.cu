@@ -134,6 +134,7 @@ struct cgb_dist {
   int4 *hplan = nullptr;
   int32_t *hoff = nullptr;
   int hplan_grid = 0, hplan_tile = 0;
+  int loop_key = 0, loop_persistent = 0; // the collective loop decision of the last solve's option set (0: none yet for this matrix)
   bool dead = false;                    // a peer wait timed out: windows and sequence numbers are inconsistent across ranks
   PeerCtx pctx() const { return PeerCtx{rank, nranks, d_win, seq}; }
 };
@@ -777,6 +778,7 @@ static void dist_release_matrix(cgb_dist *d) {
   d->hplan = nullptr;
   d->hoff = nullptr;
   d->hplan_grid = d->hplan_tile = 0;
+  d->loop_key = 0;
   d->pfull = nullptr;
   d->allgather = false;
   d->Aloc = d->Ahalo = nullptr;

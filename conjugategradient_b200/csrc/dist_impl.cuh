@@ -88,8 +88,9 @@ int all_sum2(cgb_dist *d, double a, double b, double *sa, double *sb) {
 long long peer_timeout_cycles(const cgb_ctx *ctx) {
   double ms = 30000.0;
   if (const char *e = getenv("CGB_PEER_TIMEOUT_MS")) ms = std::max(1.0, atof(e));
-  int khz = 0;
-  if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) != cudaSuccess || khz <= 0) khz = 2000000;
+  static int khz_of[64] = {}; // asked once per device: the attribute goes through the driver, this runs once per solve
+  int &khz = khz_of[ctx->device & 63];
+  if (khz <= 0 && (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) != cudaSuccess || khz <= 0)) khz = 2000000;
   return (long long)(ms * (double)khz);
 }
 
@@ -568,8 +569,18 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   // Collective decisions, and the barrier that keeps rank skew out of the in-kernel waits: the host work above
   // (engine preparation, allocations, lazy module loads) takes a different time on every rank, and the first peer
   // kernel below waits for its peers with a time limit.
+  // (Collective once per matrix and option set: repeated solves of the same system re-use the answer, which keeps an
+  // NCCL round trip and two host synchronisations out of short solves.)
+  const int okey = 1 + o.loop_mode + 16 * (o.time_kernels != 0) + 32 * (o.jacobi != 0) + 64 * (o.residual_replace_every > 0) +
+                   128 * (o.fuse_p_update != 0);
   int persistent = 0;
-  CGB_TRY(all_agree(d, dist_persistent_eligible(d, o) ? 1 : 0, &persistent));
+  if (d->loop_key == okey) {
+    persistent = d->loop_persistent;
+  } else {
+    CGB_TRY(all_agree(d, dist_persistent_eligible(d, o) ? 1 : 0, &persistent));
+    d->loop_key = okey;
+    d->loop_persistent = persistent;
+  }
   if (o.loop_mode == CGB_LOOP_PERSISTENT && !persistent)
     return fail(CGB_ERR_UNSUPPORTED, "cgb_dist_cg_solve: CGB_LOOP_PERSISTENT needs the peer transport, the TMA row engine on every rank and a small halo part");
 

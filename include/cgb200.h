@@ -283,8 +283,14 @@ int cgb_csr_from_mm_file(cgb_ctx *ctx, const char *path, cgb_csr **out);
 /* ---- row-partitioned multi-GPU (new; the reference is single-device) -------------------------
  * One process per GPU.  Rank r owns the contiguous global rows [row_begin, row_end); its local
  * CSR (cgb_csr with n = row_end-row_begin rows and GLOBAL column indices) is split into interior
- * and halo parts, remote entries of p travel as halos over NCCL (NVLink), the two scalars per
- * iteration go through ncclAllReduce. */
+ * and halo parts.  Default transport: peer memory over NVLink (cudaIpc windows) inside the library's
+ * own kernels -- boundary entries of p are stored straight into the owners' halo buffers, the two
+ * scalars per iteration are all-reduced through per-rank slots and flags; for stencil-like blocks the
+ * whole solve is ONE persistent cooperative kernel per rank.  NCCL carries the set-up exchanges and
+ * is the fallback transport (CGB_DIST_TRANSPORT=nccl).  All cgb_dist_* calls are collective: every
+ * rank makes the same calls in the same order.  A peer that does not answer within
+ * CGB_PEER_TIMEOUT_MS (default 30000) makes the solve return CGB_ERR_NCCL and the handle unusable
+ * (CGB_ERR_STATE afterwards): destroy it on every rank. */
 #define CGB_NCCL_ID_BYTES 128
 int cgb_nccl_unique_id(void *h_id128);
 /* row_starts: nranks+1 global row offsets (same on every rank). */

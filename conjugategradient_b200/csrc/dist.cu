@@ -4,11 +4,15 @@
 // is split once, on the device, into
 //   A_loc  : all local rows, only the columns it owns (indices rebased to the block), and
 //   A_halo : only the rows that touch remote columns, indices into a compact halo buffer.
-// Per iteration (peer transport, the default; peer.cuh): p-update -> pack kernel stores the boundary
-// entries of p into the owners' halo buffers over NVLink and raises their flags -> A_loc SpMV (the
-// transfer overlaps it) -> halo kernel waits for its flags, adds the A_halo correction to Ap and
-// p.Ap and all-reduces p.Ap in its last CTA -> r update + r.r, all-reduced in the last CTA, which
-// also advances the state.  Five launches, no library collective in the loop.
+// Per iteration (peer transport, the default; peer.cuh): p-update -> pack: the boundary entries of p
+// are stored into the owners' halo buffers over NVLink and the owners' flags raised -> A_loc SpMV
+// (the transfer overlaps it) -> halo part: wait for the flags, add the A_halo correction to Ap and
+// p.Ap -> all-reduce p.Ap through per-rank slots and flags -> r update + r.r, all-reduced the same
+// way, stop rule.  No library collective in the loop.  Three loops run this (chosen collectively):
+//   dist_persistent.cuh  the whole solve as ONE cooperative kernel per rank (stencil-like blocks)
+//   all-gather mode      blocks coupled to most of the vector keep their global columns; every rank
+//                        stores its slice of p into every rank's full-length copy (dist_setup_allgather)
+//   dist_enqueue_iteration  five launches per trip inside a CUDA graph (everything else, NCCL transport)
 // NCCL transport (fallback when cudaIpc peer mapping is unavailable, CGB_DIST_TRANSPORT=nccl, and
 // the comparison point): ncclSend/Recv on a side stream + two ncclAllReduce + a state kernel.
 // NCCL is resolved with dlopen so single-GPU users never need it; it always carries the set-up

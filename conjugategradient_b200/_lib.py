@@ -105,6 +105,7 @@ SIGNATURES = {
     "cgb_cg_solve": (C.c_int, [c_vp, c_vp, c_vp, c_vp, C.c_double, c_i64, C.POINTER(CgOpts), C.POINTER(CgStats)]),
     "cgb_cg_solve_host": (C.c_int, [c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_double, c_i64,
                                     C.POINTER(CgOpts), C.POINTER(CgStats)]),
+    "cgb_cg_solve_static": (C.c_int, [c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_double, c_i64, C.POINTER(CgStats)]),
     "cgb_cg_history": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.POINTER(c_i64)]),
     "cgb_residual": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_dp, c_dp]),
     "cgb_memory_footprint": (C.c_size_t, [c_i64, c_i64]),

@@ -240,6 +240,34 @@ int cgb_cg_solve_host(cgb_ctx *ctx, int64_t n, int64_t nnz, const double *h_vals
 /* r.r history of the last solve on A with record_history: h_out[k] = r.r after k trips. */
 int cgb_cg_history(cgb_ctx *ctx, cgb_csr *A, double *h_out, int64_t capacity, int64_t *count);
 
+/* ---- a solve that allocates nothing ---------------------------------------------------------------
+ * No counterpart in the reference (its solve allocates every work vector afresh, src/CG.hpp:276-301); added for
+ * hosts that cannot let this library allocate device memory: applications that hand (nearly) all of the GPU's
+ * memory to their own pool at start-up, so that a later cudaMalloc from a plugin fails; time-step loops that cannot
+ * afford the device-wide synchronisation of cudaMalloc / cudaFree; deployments that forbid driver allocations after
+ * initialisation.  cgb_cg_solve keeps r, p, A p, the solver state and the reduction partials in memory it allocates
+ * on first use; this entry point keeps them in a fixed work area inside the library image instead: a __device__
+ * array of CGB_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits.  It makes
+ * no call to cudaMalloc, cudaFree or any allocating routine, creates no stream or event, and needs no cgb_ctx and
+ * no cgb_csr: the caller passes its own device arrays (CSR with 32-bit indices, b, x; x in = initial guess,
+ * out = solution, 16-byte aligned) and a cudaStream_t of the CURRENT device (NULL = the default stream).
+ *   - Limit: n <= CGB_STATIC_MAX_ROWS (the range where cgb_cg_solve itself uses the one-kernel loop); a larger
+ *     system is refused with CGB_ERR_UNSUPPORTED and a message that names the limit.  nnz is not limited by the
+ *     work area (the matrix is the caller's).
+ *   - The first call on each device looks up the work area's device address (once per device, with that device
+ *     current).  Make that first call during start-up, before any stream capture begins.
+ *   - One work area per device, shared by all calls, never cleared between them: each call resets what must start
+ *     from zero itself.  Two calls that overlap on the same GPU (two host threads, two streams) race on it and give
+ *     wrong results; run them one after the other.  The call returns after the solve has finished (it reads the
+ *     final state back), so calls made from one thread never overlap.
+ *   - Same kernels, stop rule and trip cap as cgb_cg_solve with CGB_LOOP_PERSISTENT (max_iter < 0: n + 1).
+ *     stats (may be NULL): iterations, rr, rr0, converged, nan_stop, kernel_launches; the timing fields stay 0. */
+#define CGB_STATIC_MAX_ROWS 131072
+#define CGB_STATIC_SCRATCH_BYTES 4260096 /* (4 * CGB_STATIC_MAX_ROWS + 8224) doubles */
+int cgb_cg_solve_static(void *stream, int64_t n, int64_t nnz, const double *d_vals, const int32_t *d_cols,
+                        const int32_t *d_rowptr, const double *d_b, double *d_x, double abs_tol, int64_t max_iter,
+                        cgb_cg_stats *stats);
+
 /* replaces: CG::accuracy (src/CG.hpp:463-515): *rr = sum (b - A x)^2, *xx = sum x^2;
  * accuracy() = |rr / xx|. */
 int cgb_residual(cgb_ctx *ctx, cgb_csr *A, const double *d_x, const double *d_b, double *rr, double *xx);

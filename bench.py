@@ -131,6 +131,34 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+L2_BYTES = 126e6  # B200 L2; decides which regime a one-kernel loop is in
+
+
+def one_kernel_roofline(cluster, world, iterations, bytes_per_iteration, ms_per_launch, us_per_iteration, peak, peak_src):
+    """Roofline block of a solve that ONE kernel (per rank) runs from start to end: its launch = all iterations.
+
+    `achieved` and `frac` are PER GPU (every rank streams 1/world of the bytes, against one GPU's peak); the aggregate
+    is kept beside them.  The regime follows from what one rank moves per iteration: below the L2 size the loop is
+    latency-bound and the figure of merit is microseconds per iteration, above it the kernel is HBM-bound."""
+    by = iterations * bytes_per_iteration
+    agg = by / (ms_per_launch * 1e6)
+    ach = agg / world
+    per_rank_iter = bytes_per_iteration / world
+    if cluster:
+        kname = "cg_cluster_kernel (whole CG loop in one 16-CTA cluster, matrix and vectors in distributed shared memory)"
+        regime = "latency-bound (working set in shared memory; no HBM traffic inside the loop)"
+    else:
+        kname = ("cg_persistent_kernel (whole CG loop, cooperative launch)" if world == 1 else
+                 "cg_dist_persistent_kernel (whole row-partitioned CG loop, one cooperative kernel per rank: pack, TMA SpMV, "
+                 "halo rows, peer all-reduces)")
+        regime = ("latency-bound (working set in L2)" if per_rank_iter <= L2_BYTES else
+                  f"hbm-bound ({per_rank_iter / 1e9:.2f} GB per rank and iteration, L2 holds {L2_BYTES / 1e6:.0f} MB)")
+    return {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "per_gpu": True, "aggregate_GBps": agg, "n_gpus": world, "peak_source": peak_src, "traffic": None,
+            "bytes_per_launch": by / world, "ms_per_launch": ms_per_launch, "share_of_iteration": 1.0,
+            "us_per_iteration": us_per_iteration, "regime": regime}
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -514,17 +542,8 @@ def run_workload(rig, args, workload, steps, warmup, e2e_steps, cpu_seconds, hea
     peak, peak_src = measured_peak()
     roof = None
     if last["loop_mode"] in (L.LOOP_PERSISTENT, L.LOOP_CLUSTER):
-        # one kernel runs the whole solve: its launch = all iterations (bandwidth fraction is not meaningful
-        # at this size -- 2.5 MB per iteration lives in L2; the figure of merit is microseconds per iteration)
-        by = last["iterations"] * b_iter(n, nnz)
-        ms1 = ms_total / steps
-        kname = ("cg_cluster_kernel (whole CG loop in one 16-CTA cluster, matrix and vectors in distributed shared memory)"
-                 if last["loop_mode"] == L.LOOP_CLUSTER else "cg_persistent_kernel (whole CG loop, cooperative launch)")
-        roof = {"bound": "hbm", "kernel": kname, "achieved": by / (ms1 * 1e6),
-                "peak": peak, "unit": "GB/s", "frac": by / (ms1 * 1e6) / peak, "peak_source": peak_src, "traffic": None,
-                "bytes_per_launch": by, "ms_per_launch": ms1, "share_of_iteration": 1.0,
-                "us_per_iteration": 1e3 * ms_total / max(iters, 1), "regime": ("latency-bound (working set in shared memory; no HBM traffic inside the loop)"
-                           if last["loop_mode"] == L.LOOP_CLUSTER else "latency-bound (working set in L2)")}
+        roof = one_kernel_roofline(last["loop_mode"] == L.LOOP_CLUSTER, world, last["iterations"], b_iter(n, nnz),
+                                   ms_total / steps, 1e3 * ms_total / max(iters, 1), peak, peak_src)
     elif world == 1:
         t_opts = S.make_opts(time_kernels=1, check_every=args.check_every)
         cap = -1 if last["iterations"] <= 16 * args.check_every else 16 * args.check_every

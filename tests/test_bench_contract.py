@@ -66,3 +66,20 @@ def test_both_arms_describe_the_same_config():
     assert not ({"where", "iterations_per_solve", "true_rel_residual", "loop", "engine", "transport"} & set(c))   # per-run facts live in `run`
     w = b.counter_w(5, 1000)
     assert w.min() >= -1.0 and w.max() < 1.0 and abs(w.mean()) < 0.1 and (b.counter_w(0, 1000)[5:] == w).all()
+
+
+def test_one_kernel_roofline_is_per_gpu():
+    """At N > 1 the roofline block of the one-kernel loop is per GPU (round 2 divided the aggregate bytes by ONE GPU's
+    peak: frac 7.93 at N = 8) and its regime follows the per-rank working set.  Figures: SCALE_r02 (C4, 8 GPUs)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    bi = b.b_iter(512 ** 3, 937951232)
+    for world, its in ((1, 290.0), (2, 593.9), (4, 1151.4), (8, 2199.5)):
+        r = b.one_kernel_roofline(False, world, 1798, bi, 1798 / its * 1e3, 1e6 / its, 6545.3, "MEASURED_PEAKS.json")
+        assert 0.9 < r["frac"] <= 1.2 and r["per_gpu"] and r["n_gpus"] == world
+        assert abs(r["aggregate_GBps"] - world * r["achieved"]) < 1e-6 * r["aggregate_GBps"]
+        assert r["regime"].startswith("hbm-bound")
+    c1 = b.one_kernel_roofline(False, 1, 366, b.b_iter(16384, 81408), 366 / 147.0, 6.8, 6545.3, "x")
+    assert c1["regime"].startswith("latency-bound") and c1["frac"] < 0.2

@@ -47,6 +47,7 @@ struct DevCache {
   std::multimap<size_t, void *> free_blocks;   // size -> block
   std::unordered_map<void *, size_t> live;     // blocks handed out
   size_t cached_bytes = 0;
+  size_t cap = 0; // most bytes kept parked on this device (0: not yet determined)
 };
 struct AllocCache {
   std::mutex mu;
@@ -54,12 +55,25 @@ struct AllocCache {
   std::multimap<size_t, void *> host_free;
   std::unordered_map<void *, size_t> host_live;
   bool on = true;
-  size_t max_bytes = (size_t)64 << 30;
+  size_t max_bytes = 0; // CGB_ALLOC_CACHE_MAX_GB; 0: per device, a quarter of its memory, at most 32 GB
   AllocCache() {
     if (const char *e = getenv("CGB_ALLOC_CACHE")) on = atoi(e) != 0;
     if (const char *e = getenv("CGB_ALLOC_CACHE_MAX_GB")) max_bytes = (size_t)(atof(e) * (double)((size_t)1 << 30));
   }
 };
+// Parked blocks are invisible to every other allocator of the process (NCCL, cub, torch, cupy): the default bound is
+// a quarter of the device's memory and never more than 32 GB -- room for the largest end-to-end case measured
+// (C4: 19.3 GB of matrix and work vectors per call) and no more.  Call with `dev` current.
+size_t device_cap(const AllocCache &c, DevCache &d) {
+  if (d.cap) return d.cap;
+  if (c.max_bytes) return d.cap = c.max_bytes;
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) {
+    cudaGetLastError();
+    total_b = (size_t)64 << 30;
+  }
+  return d.cap = std::min((size_t)32 << 30, total_b / 4);
+}
 AllocCache &alloc_cache() {
   static AllocCache *c = new AllocCache(); // never destroyed: frees may come from static destructors
   return *c;
@@ -123,11 +137,13 @@ cudaError_t cached_free(void *p) {
   const size_t sz = it->second;
   d.live.erase(it);
   lk.unlock();
+  ScopedDevice sd(dev); // the block's device, whatever the caller has current
   cudaError_t e = cudaDeviceSynchronize(); // cudaFree's semantics: nothing in flight touches the block once it changes hands
   lk.lock();
   d.free_blocks.emplace(sz, p);
   d.cached_bytes += sz;
-  if (d.cached_bytes > c.max_bytes) trim_device_locked(d, c.max_bytes);
+  const size_t cap = device_cap(c, d);
+  if (d.cached_bytes > cap) trim_device_locked(d, cap);
   return e;
 }
 
@@ -193,8 +209,8 @@ constexpr size_t kStageMin = (size_t)8 << 20;
 constexpr size_t kStageChunk = (size_t)4 << 20;
 constexpr int kStageWorkersMax = 8;
 
-struct Stager {
-  std::mutex mu; // one staged copy at a time per process
+struct Stager { // one per device: streams, events and bounce buffers live in that device's context
+  std::mutex mu; // one staged copy at a time per device
   int device = -1;
   int workers = 0;
   void *buf[kStageWorkersMax][2] = {};
@@ -203,29 +219,56 @@ struct Stager {
   cudaStream_t st[kStageWorkersMax] = {};
   cudaEvent_t start = nullptr;
   bool ok = false;
+  bool failed = false; // set-up failed once: this device keeps the driver's path, no retry
 };
-Stager &stager() {
-  static Stager *s = new Stager();
+Stager &stager(int device) {
+  static std::mutex mu;
+  static std::map<int, Stager *> *all = new std::map<int, Stager *>(); // never destroyed (copies may run from static destructors)
+  std::lock_guard<std::mutex> lk(mu);
+  Stager *&s = (*all)[device];
+  if (!s) s = new Stager();
   return *s;
 }
 
+// give back whatever a failed set-up had created
+void stager_release(Stager &s) {
+  for (int i = 0; i < kStageWorkersMax; i++) {
+    for (int b = 0; b < 2; b++) {
+      if (s.buf[i][b]) cudaFreeHost(s.buf[i][b]);
+      if (s.ev[i][b]) cudaEventDestroy(s.ev[i][b]);
+      s.buf[i][b] = nullptr;
+      s.ev[i][b] = nullptr;
+    }
+    if (s.done[i]) cudaEventDestroy(s.done[i]);
+    if (s.st[i]) cudaStreamDestroy(s.st[i]);
+    s.done[i] = nullptr;
+    s.st[i] = nullptr;
+  }
+  if (s.start) cudaEventDestroy(s.start);
+  s.start = nullptr;
+  cudaGetLastError();
+}
+
+// called with s.mu held and `device` current
 bool stager_init(Stager &s, int device) {
-  if (s.ok && s.device == device) return true;
-  if (s.ok) return false; // bound to another device: that caller takes the driver's path
+  if (s.ok) return true;
+  if (s.failed) return false;
   int hw = (int)std::thread::hardware_concurrency();
   int w = hw >= 16 ? 6 : hw >= 8 ? 4 : 2;
   if (const char *e = getenv("CGB_STAGE_THREADS")) w = std::max(1, std::min(kStageWorkersMax, atoi(e)));
-  if (cudaEventCreateWithFlags(&s.start, cudaEventDisableTiming) != cudaSuccess) return false;
-  for (int i = 0; i < w; i++) {
-    bool good = cudaStreamCreateWithFlags(&s.st[i], cudaStreamNonBlocking) == cudaSuccess &&
-                cudaEventCreateWithFlags(&s.done[i], cudaEventDisableTiming) == cudaSuccess;
+  bool good = cudaEventCreateWithFlags(&s.start, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < w && good; i++) {
+    good = cudaStreamCreateWithFlags(&s.st[i], cudaStreamNonBlocking) == cudaSuccess &&
+           cudaEventCreateWithFlags(&s.done[i], cudaEventDisableTiming) == cudaSuccess;
     for (int b = 0; b < 2 && good; b++)
       good = cudaMallocHost(&s.buf[i][b], kStageChunk) == cudaSuccess &&
              cudaEventCreateWithFlags(&s.ev[i][b], cudaEventDisableTiming) == cudaSuccess;
-    if (!good) {
-      cudaGetLastError();
-      return false;
-    }
+  }
+  if (!good) {
+    cudaGetLastError();
+    stager_release(s);
+    s.failed = true;
+    return false;
   }
   s.workers = w;
   s.device = device;
@@ -246,8 +289,9 @@ bool host_is_pageable(const void *p) {
 bool staged_copy(cgb_ctx *ctx, void *d, void *h, size_t bytes, bool to_device, cudaError_t *err) {
   if (const char *e = getenv("CGB_STAGE"))
     if (atoi(e) == 0) return false;
-  Stager &s = stager();
+  Stager &s = stager(ctx->device);
   std::lock_guard<std::mutex> lk(s.mu);
+  ScopedDevice sd(ctx->device);
   if (!stager_init(s, ctx->device)) return false;
   const size_t nchunks = (bytes + kStageChunk - 1) / kStageChunk;
   const int W = (int)std::min<size_t>((size_t)s.workers, nchunks);

@@ -497,6 +497,7 @@ int cgb_dist_create(cgb_ctx *ctx, int rank, int nranks, const void *h_id128, con
   do {
     ncclUniqueId id;
     memcpy(&id, h_id128, sizeof(id));
+    cache_trim(); // NCCL allocates its buffers with the driver: blocks parked in the library's cache must not starve it
     ncclResult_t r = g_nccl.CommInitRank(&d->comm, nranks, id, rank);
     if (r != ncclSuccess) {
       rc = fail(CGB_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
@@ -577,6 +578,12 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
   if (d->loop_key == okey) {
     persistent = d->loop_persistent;
   } else {
+    // every rank must have passed the same options: sum k = N k and sum k^2 = N k^2 only if all k are equal
+    double sk = 0.0, sk2 = 0.0;
+    CGB_TRY(all_sum2(d, (double)okey, (double)okey * okey, &sk, &sk2));
+    if (sk != (double)d->nranks * okey || sk2 != (double)d->nranks * okey * okey)
+      return fail(CGB_ERR_INVALID, "cgb_dist_cg_solve: the ranks passed different options (loop_mode, time_kernels, jacobi, "
+                  "residual_replace_every, fuse_p_update must be the same on every rank)");
     CGB_TRY(all_agree(d, dist_persistent_eligible(d, o) ? 1 : 0, &persistent));
     d->loop_key = okey;
     d->loop_persistent = persistent;
@@ -709,6 +716,7 @@ int cgb_dist_cg_solve(cgb_dist *d, const double *d_b, double *d_x, double abs_to
 
 int cgb_dist_residual(cgb_dist *d, const double *d_x, const double *d_b, double *rr, double *xx) {
   CGB_REQUIRE(d && d_x && d_b && rr && xx, "cgb_dist_residual: NULL argument");
+  CGB_REQUIRE(((uintptr_t)d_x & 15) == 0, "cgb_dist_residual: x must be 16-byte aligned (128-bit vector accesses)");
   cgb_ctx *ctx = d->ctx;
   cgb_csr *A = d->Aloc;
   ScopedDevice sd(ctx->device);

@@ -73,7 +73,7 @@ struct DistLoopArgs {
   long long timeout_cycles;
   int vec_tma;                   // the vector passes through TMA-staged tiles (long vectors) or grid-stride loops (short ones)
   int phase_timing;              // CGB_DIST_TIMING: CTA 0 stamps the phases (globaltimer)
-  int side_pack;                 // the pack's fence / ticket / flags on the producer warp's idle lane (1) or inline before the tiles (0, A/B)
+  int side_pack;                 // the pack's fence / ticket / flags on the producer lane behind its first tiles (1) or inline before the tiles (0, A/B)
   unsigned jitter_ns;            // CGB_DIST_JITTER_NS (tests): every CTA sleeps a pseudo-random time below this before each phase
 };
 
@@ -268,7 +268,7 @@ __device__ __forceinline__ int ld_keep_s32(const int *p, uint64_t pol) {
   return v;
 }
 
-// Second half of the halo pack, run by an idle lane of the TMA engine's producer warp while the tiles stream: order the
+// Second half of the halo pack, run by the TMA engine's producer lane once its first tiles are in flight: order the
 // CTA's peer stores (they precede the CTA barrier that opened the tile loop, so this thread's fence is cumulative over
 // them), take the ticket, and in the CTA that finishes last raise this rank's flag in every destination window.
 struct PackFinish {

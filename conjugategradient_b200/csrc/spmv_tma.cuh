@@ -115,8 +115,8 @@ struct TmaNoSideJob {
 };
 
 // Must be called by all kTmaThreads threads of the CTA.  `smem_raw` is the dynamic shared memory.
-// `side` runs once on the second lane of the producer warp (which is otherwise idle) while the tiles stream: the
-// persistent multi-GPU loop hides the system-scope fence and the flag stores of its halo pack there.
+// `side` runs once per CTA on the producer lane, after it has put the first kTmaStages tiles in flight: the persistent
+// multi-GPU loop hides the system-scope fence and the flag stores of its halo pack there.
 template <int L, class G, class E, class SIDE = TmaNoSideJob>
 __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int *__restrict__ rowptr,
                                               const int *__restrict__ cols, const double *__restrict__ vals,
@@ -142,9 +142,13 @@ __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int 
   __syncthreads();
 
   if (tid >= kTmaConsumers) {
-    if (tid == kTmaConsumers + 1) side();
     // ---------------- producer warp: one lane drives the TMA ----------------
+    // The side job runs on this same lane once the pipeline is primed (kTmaStages tiles in flight), so its latency
+    // (a system-scope fence and a ticket in the multi-GPU pack) lies behind the consumers' work on those tiles.  On
+    // another lane of this warp it would run first: the two branches of a warp do not overlap, and the fence would
+    // sit in front of tile 0.
     if (tid == kTmaConsumers) {
+      int primed = 0;
       const uint64_t pol = l2_policy_evict_first();
       int stage = 0;
       uint32_t phase = 0;
@@ -197,7 +201,9 @@ __device__ __forceinline__ void spmv_rows_tma(int64_t n, int64_t nnz, const int 
           stage = 0;
           phase ^= 1;
         }
+        if (++primed == kTmaStages) side();
       }
+      if (primed < kTmaStages) side(); // fewer tiles than stages (or none) for this CTA
     }
   } else {
     // ---------------- consumers ----------------

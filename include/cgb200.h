@@ -73,8 +73,11 @@ int cgb_free(cgb_ctx *ctx, void *d_ptr);
  * per-device cache of whole allocations and handed out again for requests of the same size, so repeated
  * host-buffer solves (cgb_cg_solve_host, cgb_dist_set_matrix) cost no driver allocation after the first; the
  * reference allocates afresh on every setMatrix / solve (src/LinearAlgebraTypes.hpp:109-119, src/CG.hpp:276-301).
- * cgb_trim returns the cached blocks to the driver (environment: CGB_ALLOC_CACHE=0 disables the cache,
- * CGB_ALLOC_CACHE_MAX_GB bounds it, default 64). */
+ * So cgb_free RETAINS memory: parked blocks are invisible to the other allocators of the process (NCCL, cub, torch,
+ * cupy), and only the library's own failed allocation trims them.  At most a quarter of the device's memory and never
+ * more than 32 GB stay parked per device (CGB_ALLOC_CACHE_MAX_GB overrides the bound, CGB_ALLOC_CACHE=0 disables the
+ * cache); cgb_trim returns the cached blocks to the driver -- call it before handing the GPU to another allocator.
+ * cgb_dist_create trims before it creates the NCCL communicator. */
 int cgb_trim(void);
 int cgb_memcpy_h2d(cgb_ctx *ctx, void *d_dst, const void *h_src, size_t bytes, int sync);
 int cgb_memcpy_d2h(cgb_ctx *ctx, void *h_dst, const void *d_src, size_t bytes, int sync);
@@ -318,7 +321,13 @@ int cgb_csr_from_mm_file(cgb_ctx *ctx, const char *path, cgb_csr **out);
  * is the fallback transport (CGB_DIST_TRANSPORT=nccl).  All cgb_dist_* calls are collective: every
  * rank makes the same calls in the same order.  A peer that does not answer within
  * CGB_PEER_TIMEOUT_MS (default 30000) makes the solve return CGB_ERR_NCCL and the handle unusable
- * (CGB_ERR_STATE afterwards): destroy it on every rank. */
+ * (CGB_ERR_STATE afterwards): destroy it on every rank.
+ * Two rules follow from the solve being collective.  (1) Every rank passes the same cgb_cg_opts: the first solve of a
+ * matrix with a given option set checks this across the ranks (CGB_ERR_INVALID on a mismatch) and remembers the
+ * loop it chose; later solves with that option set skip the check and its host barrier, so a rank that changes its
+ * options alone afterwards waits in a collective the others never enter.  (2) Without that barrier the ranks must
+ * enter a repeated solve within CGB_PEER_TIMEOUT_MS of each other: an application with long, uneven host phases
+ * between solves (file output on one rank) raises the limit or synchronises its ranks itself before the call. */
 #define CGB_NCCL_ID_BYTES 128
 int cgb_nccl_unique_id(void *h_id128);
 /* row_starts: nranks+1 global row offsets (same on every rank). */

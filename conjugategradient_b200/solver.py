@@ -368,9 +368,23 @@ def mm_read(path: str):
 
 
 # ---- row-partitioned multi-GPU (one process per GPU; new) ---------------------------
-def partition_rows(n: int, world: int, align: int = 1, rowptr=None) -> np.ndarray:
+def partition_rows(n: int, world: int, align: int = 1, rowptr=None, edge_extra: int = 0) -> np.ndarray:
     """world+1 global row offsets of contiguous row blocks.  Balanced by rows (multiples of `align`,
-    e.g. one grid plane for a stencil) or, when `rowptr` is given, by non-zeros."""
+    e.g. one grid plane for a stencil) or, when `rowptr` is given, by non-zeros.
+
+    edge_extra (rows; world >= 3 only): the first and the last rank get this many more rows than the others.  In a
+    slab decomposition of a stencil they have one neighbour instead of two (one halo plane to pack, send and apply),
+    finish each trip early and wait in the all-reduce; the extra rows even the trip time out."""
+    if rowptr is None and edge_extra > 0 and world >= 3:
+        units, extra = n // align, edge_extra // align
+        inner = max((units - 2 * extra) // world, 0)
+        sizes = [inner + extra] + [inner] * (world - 2) + [inner + extra]
+        left = units - sum(sizes)           # hand the remainder out from the middle
+        for k in range(left):
+            sizes[1 + (k % (world - 2))] += 1
+        starts = align * np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        starts[-1] = n
+        return starts
     if rowptr is not None:
         rp = np.asarray(rowptr, dtype=np.int64)
         targets = rp[-1] * np.arange(1, world, dtype=np.float64) / world

@@ -36,6 +36,11 @@ def plan_halo(rank, world, starts, cols):
 def test_partition_rows():
     assert list(S.partition_rows(10, 3)) == [0, 3, 6, 10]
     assert list(S.partition_rows(512 ** 3, 8, align=512 * 512)) == [k * 64 * 512 * 512 for k in range(9)]
+    st = S.partition_rows(512 ** 3, 8, align=512, edge_extra=int(1.25 * 512 * 512))    # edge ranks: one halo plane, more rows
+    sz = np.diff(st)
+    assert st[0] == 0 and st[-1] == 512 ** 3 and (sz % 512 == 0).all() and sz[0] == sz[-1]
+    assert sz[0] - sz[1:-1].max() in (int(1.25 * 512) * 512 - 512, int(1.25 * 512) * 512) and sz[1:-1].max() - sz[1:-1].min() <= 512
+    assert list(S.partition_rows(10, 2, edge_extra=4)) == [0, 5, 10]                     # two ranks: both are edges
     st = S.partition_rows(27, 4, align=9)                  # 3 planes over 4 ranks: one rank gets nothing
     assert st[0] == 0 and st[-1] == 27 and np.all(np.diff(st) >= 0) and np.all(st % 9 == 0)
     v, c, r = G.random_spd_powerlaw(5000, seed=1)

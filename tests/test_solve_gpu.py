@@ -283,7 +283,13 @@ def test_full_size_properties_C4(ctx):
     cg.setMatrix(A)
     cg.setTarget(b)
     st = cg.solve(1e-8 * nb)
-    assert st["converged"] == 1 and 1700 <= st["iterations"] <= 1900              # 1798 on every run so far
+    # the reference's own trip count for this solve (oracle/_ref run to convergence on the CPU once, committed by
+    # tools/make_bench_parity.py --full): north_star's +-2 %
+    import json
+    ref_full = json.load(open(os.path.join(GOLD, "bench_parity.json")))["poisson3d_7pt_512"]["full"]
+    assert st["converged"] == 1 and iters_close(st["iterations"], ref_full["iterations"]), (st["iterations"], ref_full["iterations"])
+    x_tol = X_RTOL if st["iterations"] == ref_full["iterations"] else 1e-7    # a trip apart: both within the solve's own tolerance
+    assert abs(np.sqrt(cg.residual()[1]) - ref_full["x_norm2"]) <= x_tol * ref_full["x_norm2"]
     rr, xx = cg.residual()
     assert np.sqrt(rr) / nb <= 2e-8
 
